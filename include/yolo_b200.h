@@ -1,0 +1,180 @@
+/*
+ * yolo_b200.h -- C ABI of libyolo_b200.so: the B200 (sm_100a) implementation of the
+ * YOLOv7 inference hot path of qbxlvnf11/yolo-series.
+ *
+ * The reference has no FFI layer: its boundary is two Python callables,
+ *   Model.forward(x, augment, profile)                   models/yolo.py:581-631
+ *   non_max_suppression(prediction, conf_thres, ...)     utils/general.py:628-720
+ * plus the head decode inside IDetect/IAuxDetect/Detect (models/yolo.py:42-77,
+ * 140-176, 364-399).  The Python shim in yolo_series_b200/ keeps those exact
+ * signatures and calls the entry points below through ctypes.  Every entry point
+ * takes raw device pointers + sizes + a cudaStream_t (passed as void*), never frees
+ * caller memory, performs no hidden synchronisation, and returns 0 on success or a
+ * negative yb_status; yb_last_error() gives the message (per thread).
+ *
+ * Layout conventions: activations are NHWC ("channels last") with an explicit
+ * channel stride so that a tensor may be a channel slice of a wider concat buffer
+ * (replaces Concat.forward = torch.cat(x, 1), models/common.py:61-62).
+ */
+#ifndef YOLO_B200_H
+#define YOLO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YB_ABI_VERSION 1
+
+typedef enum {
+  YB_OK = 0,
+  YB_ERR_INVALID = -1,   /* bad argument / unsupported shape */
+  YB_ERR_CUDA = -2,      /* a CUDA runtime/driver call failed */
+  YB_ERR_WORKSPACE = -3, /* caller workspace too small */
+  YB_ERR_OVERFLOW = -4,  /* candidate capacity exceeded (see yb_nms) */
+  YB_ERR_UNSUPPORTED = -5
+} yb_status;
+
+typedef enum { YB_F32 = 0, YB_BF16 = 1, YB_U8 = 2 } yb_dtype;
+typedef enum { YB_ACT_NONE = 0, YB_ACT_SILU = 1, YB_ACT_LEAKY = 2 } yb_act;
+
+const char* yb_last_error(void);
+int yb_abi_version(void);
+
+/* ------------------------------------------------------------------ tensors */
+/* NHWC view: element (n,h,w,c) lives at data + ((n*H + h)*W + w)*c_stride + c   (in elements) */
+typedef struct {
+  void* data;       /* device pointer, already offset to channel 0 of the view */
+  int32_t dtype;    /* yb_dtype */
+  int32_t N, H, W, C;
+  int32_t c_stride; /* channels of the underlying buffer (>= C) */
+} yb_tensor;
+
+/* ------------------------------------------------------------------ conv
+ * Replaces Conv.fuseforward = act(conv2d(x, W', b')) (models/common.py:110-111), the fused
+ * RepConv (common.py:498-500) and the 1x1 head convs (models/yolo.py:145), with BN / RepVGG /
+ * Implicit folding done on the host at load time (utils/torch_utils.py:181-201,
+ * common.py:584-643, yolo.py:178-190).
+ *   k in {1,3}, stride in {1,2}, pad = k/2, groups = 1.
+ *   weight layout: [Cout_pad][k*k][Cin_pad]  ("KRSC"), dtype = x.dtype; bias: fp32 [Cout_pad].
+ *   upsample = 2 writes every output pixel to the 2x2 block it maps to under
+ *   nn.Upsample(None, 2, 'nearest') (cfg/training/yolov7.yaml:78) -- y then has 2H x 2W.
+ *   bf16 x  -> tcgen05/TMEM implicit-GEMM kernel (fp32 accumulate); y may be bf16 or fp32.
+ *   fp32 x  -> fp32 CUDA-core reference-mode kernel; y fp32.
+ */
+typedef struct {
+  yb_tensor x, y;
+  const void* weight;
+  const float* bias;
+  int32_t cin_pad, cout_pad; /* padded extents of the weight array */
+  int32_t k, stride;
+  int32_t act;               /* yb_act */
+  float leaky_slope;
+  int32_t upsample;          /* 1 or 2 */
+  /* optional residual: y = act(conv) + res (Shortcut, models/common.py:85-86); data==NULL -> none */
+  yb_tensor res;
+  /* tuning overrides, 0 = auto */
+  int32_t tile_n, stages;
+} yb_conv_desc;
+
+int yb_conv2d(const yb_conv_desc* d, void* stream);
+
+/* ------------------------------------------------------------------ pooling / data movement */
+/* MP: MaxPool2d(2,2) (models/common.py:30-36) */
+int yb_maxpool2x2(const yb_tensor* x, const yb_tensor* y, void* stream);
+/* SP: MaxPool2d(k, 1, k/2) with -inf padding (models/common.py:39-45), k odd <= 13 */
+int yb_maxpool_s1(const yb_tensor* x, const yb_tensor* y, int k, void* stream);
+/* SPPCSPC.m: the k=5,9,13 stride-1 pools of one tensor in a single pass (models/common.py:271,278) */
+int yb_spp3(const yb_tensor* x, const yb_tensor* y5, const yb_tensor* y9, const yb_tensor* y13, void* stream);
+/* nn.Upsample(None, 2, 'nearest') stand-alone */
+int yb_upsample2x(const yb_tensor* x, const yb_tensor* y, void* stream);
+/* channel-slice copy (Concat fallback when a producer cannot write in place) */
+int yb_copy(const yb_tensor* x, const yb_tensor* y, void* stream);
+/* Shortcut: y = a + b (models/common.py:85-86) */
+int yb_add(const yb_tensor* a, const yb_tensor* b, const yb_tensor* y, void* stream);
+
+/* Input staging: NCHW image (uint8 0..255 or float 0..1, B x C x H x W) -> NHWC y (bf16 or fp32,
+ * y.C >= C, extra channels zero).  uint8 is scaled by 1/255 (detect.py:100-104).
+ * reorg != 0 fuses ReOrg (models/common.py:52-53): y is (B, H/2, W/2, >= 4C) with channel
+ * block order (even,even),(odd,even),(even,odd),(odd,odd) in (row,col) parity. */
+int yb_stage_input(const void* img, int img_dtype, int B, int C, int H, int W, int reorg,
+                   const yb_tensor* y, void* stream);
+
+/* ------------------------------------------------------------------ head decode
+ * IDetect.fuseforward inference branch (models/yolo.py:145-162; arithmetic SURVEY.md A.5).
+ * Each level: logits NHWC (B, ny, nx, >= na*no), channel index a*no + o.
+ * pred: (B, A, no) fp32, A = na * sum(ny*nx), rows level-major then (a, gy, gx).
+ * raw[l] (nullable array / nullable entries): (B, na, ny, nx, no) fp32 un-activated logits
+ * (the second return value, yolo.py:147-148).
+ */
+#define YB_MAX_LEVELS 8
+#define YB_MAX_ANCHORS 8
+typedef struct {
+  yb_tensor logits;
+  float stride;
+  float anchor_wh[2 * YB_MAX_ANCHORS]; /* anchor_grid in pixels */
+} yb_head_level;
+
+int yb_decode(const yb_head_level* levels, int nl, int na, int no, float* pred, float* const* raw,
+              void* stream);
+
+/* ------------------------------------------------------------------ NMS
+ * non_max_suppression (utils/general.py:628-720) + torchvision.ops.nms (general.py:704):
+ *   candidate filter obj > conf_thres, conf = obj*cls (nc==1: conf = obj), xywh->xyxy,
+ *   best-class or multi-label expansion, optional class whitelist, stable descending sort,
+ *   top-max_nms cut, class-offset (4096 px) greedy IoU suppression with the threshold compared
+ *   in double, max_det cut.  Results are bit-identical to the reference on identical fp32 input.
+ * pred: (B, A, no) fp32.  out: (B, max_det, 6) fp32 rows [x1,y1,x2,y2,conf,cls]; counts: (B) int32.
+ * classes: host array (nullable).  cand_cap: per-image candidate capacity the workspace was sized
+ *   for (0 -> A, or A*nc when multi_label); if an image produces more, YB_ERR_OVERFLOW is reported
+ *   through *overflow (device int, nullable) -- the call itself never synchronises.
+ */
+size_t yb_nms_workspace_bytes(int B, int A, int no, int multi_label, int cand_cap);
+int yb_nms(const float* pred, int B, int A, int no, float conf_thres, double iou_thres,
+           const int* classes, int n_classes, int agnostic, int multi_label, int max_nms, int max_det,
+           int cand_cap, void* workspace, size_t workspace_bytes, float* out, int* counts,
+           int* overflow, void* stream);
+
+/* Fused decode -> candidate filter -> NMS: same result as yb_decode followed by yb_nms, without
+ * materialising pred in HBM (the north-star's "one fused decode kernel ... threshold compaction"). */
+int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no, float conf_thres,
+                  double iou_thres, const int* classes, int n_classes, int agnostic, int multi_label,
+                  int max_nms, int max_det, int cand_cap, void* workspace, size_t workspace_bytes,
+                  float* out, int* counts, int* overflow, void* stream);
+
+/* ------------------------------------------------------------------ engine (Model.forward)
+ * A flat launch list produced by the host-side graph lowering of Model.model
+ * (models/yolo.py:601-631 forward_once).  Tensors and weights are caller-owned device memory.
+ */
+typedef enum {
+  YB_OP_CONV = 1, YB_OP_MAXPOOL2 = 2, YB_OP_POOL_S1 = 3, YB_OP_SPP3 = 4, YB_OP_UPSAMPLE2 = 5,
+  YB_OP_COPY = 6, YB_OP_ADD = 7
+} yb_op_kind;
+
+typedef struct {
+  int32_t kind;           /* yb_op_kind */
+  int32_t in0, in1;       /* tensor indices (-1 = unused) */
+  int32_t out0, out1, out2;
+  int32_t k, stride, act, upsample;
+  float leaky_slope;
+  int32_t weight;         /* index into weights/biases (-1 = none) */
+  int32_t cin_pad, cout_pad;
+  int32_t tile_n, stages; /* 0 = auto */
+} yb_op;
+
+typedef struct yb_engine yb_engine;
+
+int yb_engine_create(const yb_tensor* tensors, int n_tensors, const yb_op* ops, int n_ops,
+                     const void* const* weights, const float* const* biases, int n_weights,
+                     yb_engine** out);
+/* launch every op on `stream`; use_graph != 0 replays a CUDA graph captured on first use */
+int yb_engine_forward(yb_engine* e, int use_graph, void* stream);
+int yb_engine_num_launches(const yb_engine* e);
+void yb_engine_destroy(yb_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YOLO_B200_H */

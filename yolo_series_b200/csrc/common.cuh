@@ -1,0 +1,80 @@
+// Shared host/device helpers for libyolo_b200.so (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/yolo_b200.h"
+
+namespace yb {
+
+void set_error(const char* fmt, ...);
+
+#define YB_CHECK_ARG(cond, ...)                     \
+  do {                                              \
+    if (!(cond)) {                                  \
+      ::yb::set_error(__VA_ARGS__);                 \
+      return YB_ERR_INVALID;                        \
+    }                                               \
+  } while (0)
+
+#define YB_CUDA(expr)                                                                        \
+  do {                                                                                       \
+    cudaError_t _e = (expr);                                                                 \
+    if (_e != cudaSuccess) {                                                                 \
+      ::yb::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return YB_ERR_CUDA;                                                                    \
+    }                                                                                        \
+  } while (0)
+
+#define YB_LAUNCH_CHECK()                                                                    \
+  do {                                                                                       \
+    cudaError_t _e = cudaGetLastError();                                                     \
+    if (_e != cudaSuccess) {                                                                 \
+      ::yb::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return YB_ERR_CUDA;                                                                    \
+    }                                                                                        \
+  } while (0)
+
+inline int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+inline size_t dtype_size(int dt) { return dt == YB_F32 ? 4 : dt == YB_BF16 ? 2 : 1; }
+
+inline bool view_ok(const yb_tensor& t) {
+  return t.data && t.N > 0 && t.H > 0 && t.W > 0 && t.C > 0 && t.c_stride >= t.C;
+}
+
+__host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// ---- dtype traits for the elementwise / stencil kernels
+template <typename T> struct Elem;
+template <> struct Elem<float> {
+  static __device__ __forceinline__ float load(const float* p) { return *p; }
+  static __device__ __forceinline__ void store(float* p, float v) { *p = v; }
+};
+template <> struct Elem<__nv_bfloat16> {
+  static __device__ __forceinline__ float load(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+  static __device__ __forceinline__ void store(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+};
+
+// internal launchers shared by the C ABI wrappers and the engine
+int conv_fp32_launch(const yb_conv_desc& d, cudaStream_t s);
+
+struct ConvTcPlan;  // opaque: tensor maps + launch geometry for one bf16 conv
+int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out);
+int conv_tc_launch(const ConvTcPlan* p, cudaStream_t s);
+void conv_tc_plan_destroy(ConvTcPlan* p);
+
+}  // namespace yb

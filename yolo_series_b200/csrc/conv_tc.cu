@@ -1,0 +1,503 @@
+// bf16 implicit-GEMM convolution on the 5th-gen tensor cores (tcgen05.mma, accumulators in TMEM),
+// operands staged by TMA.  Replaces Conv.fuseforward / fused RepConv / head 1x1 convs of the
+// reference (models/common.py:110-111, 498-500; models/yolo.py:145) after host-side folding.
+//
+// GEMM view:  D[pixel][cout] = sum_{tap, cin} X[pixel shifted by tap][cin] * W[cout][tap][cin]
+//   M tile = 128 output pixels = a BW x BH spatial box of one image (or 128 consecutive pixels of
+//            the flattened N*H*W axis for 1x1/s1 convs), loaded per filter tap with a 4-D TMA box
+//            whose negative / overflowing coordinates are zero-filled by the hardware (= conv padding);
+//            stride-2 convs use the tensor map's elementStrides.
+//   N tile = BN output channels (32/64/128/256), weights [Cout][taps][Cin] loaded with a 3-D TMA box.
+//   K loop = taps x ceil(Cin/BK) chunks, BK = 64/32/16 channels (SWIZZLE_128B/64B/32B, K-major).
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM alloc), warps 2..5 = epilogue
+// (tcgen05.ld -> +bias -> SiLU/LeakyReLU -> bf16/fp32 -> swizzled smem -> TMA store).  The store
+// tensor map addresses a channel slice of the consumer's concat buffer (Concat fused away) and, for
+// convs feeding nn.Upsample, four maps with doubled strides write the 2x2 replicas.
+#include <cuda.h>
+
+#include "common.cuh"
+
+namespace yb {
+
+struct ConvTcArgs {
+  CUtensorMap tm_a;
+  CUtensorMap tm_b;
+  CUtensorMap tm_y[4];
+  const float* bias;
+  int tiles_n, tiles_w, tiles_h;   // tile grid; m tiles = tiles_w * tiles_h * images
+  int BW, BH, BN, BK;              // spatial box, N tile, K chunk (channels)
+  int taps, ksz, stride, pad;
+  int kchunks;                     // ceil(Cin / BK)
+  int stages;
+  int act; float slope;
+  int n_store_maps;                // 1 or 4 (upsample)
+  int out_f32;
+  int flat;                        // 1: M axis is the flattened pixel list
+  int sw_mode;                     // UMMA layout type: 2 = SW128, 4 = SW64, 6 = SW32
+  int tmem_cols;
+  int bias_len;
+  uint32_t idesc;
+};
+
+// ------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(const CUtensorMap* tm, uint32_t bar, uint32_t dst, int c0, int c1, int c2,
+                                            int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(const CUtensorMap* tm, uint32_t bar, uint32_t dst, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(tm), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
+//   [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout type
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t sbo_bytes, uint32_t layout_type) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)(layout_type & 7) << 61;
+  return d;
+}
+
+__device__ __forceinline__ float act_fast(float v, int act, float slope) {
+  if (act == YB_ACT_SILU) return __fdividef(v, 1.0f + __expf(-v));
+  if (act == YB_ACT_LEAKY) return v > 0.f ? v : v * slope;
+  return v;
+}
+
+constexpr int kTcThreads = 192;
+
+__global__ void __launch_bounds__(kTcThreads) k_conv_tc(const __grid_constant__ ConvTcArgs G) {
+  extern __shared__ unsigned char smem_dyn[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // ---- carve shared memory: [tiles (1024-aligned)] [barriers] [tmem ptr] [bias]
+  const uint32_t raw = smem_u32(smem_dyn);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;
+  unsigned char* tiles_ptr = smem_dyn + (tiles - raw);
+  const uint32_t a_bytes = 128u * G.BK * 2u;
+  const uint32_t b_bytes = (uint32_t)G.BN * G.BK * 2u;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t out_es = G.out_f32 ? 4u : 2u;
+  uint32_t pipe_bytes = stage_bytes * G.stages;
+  const uint32_t stage_out_bytes = 128u * G.BN * out_es;
+  if (pipe_bytes < stage_out_bytes) pipe_bytes = stage_out_bytes;
+  unsigned char* aux = tiles_ptr + pipe_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(aux);            // full[stages], empty[stages], tmem_full
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux + 8 * (2 * G.stages + 1));
+  float* bias_s = reinterpret_cast<float*>(aux + 8 * (2 * G.stages + 1) + 16);
+  const uint32_t bar_full0 = smem_u32(bars), bar_empty0 = bar_full0 + 8u * G.stages;
+  const uint32_t bar_tmem = bar_full0 + 16u * G.stages;
+
+  // ---- tile coordinates
+  const int n_tile = blockIdx.x % G.tiles_n;
+  int m_tile = blockIdx.x / G.tiles_n;
+  const int tw = m_tile % G.tiles_w;
+  m_tile /= G.tiles_w;
+  const int th = m_tile % G.tiles_h;
+  const int img = m_tile / G.tiles_h;
+  const int n0 = n_tile * G.BN;
+  const int w0 = tw * G.BW, h0 = th * G.BH;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&G.tm_a);
+    tma_prefetch_desc(&G.tm_b);
+    for (int i = 0; i < G.n_store_maps; ++i) tma_prefetch_desc(&G.tm_y[i]);
+    for (int s = 0; s < G.stages; ++s) { mbar_init(bar_full0 + 8u * s, 1); mbar_init(bar_empty0 + 8u * s, 1); }
+    mbar_init(bar_tmem, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)G.tmem_cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (warp >= 2) {
+    for (int i = threadIdx.x - 64; i < G.BN; i += 128) bias_s[i] = (n0 + i < G.bias_len) ? G.bias[n0 + i] : 0.f;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+  const int total_chunks = G.taps * G.kchunks;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      const uint32_t tx = (uint32_t)(G.BW * G.BH) * G.BK * 2u + b_bytes;
+      int kc = 0;
+      for (int tap = 0; tap < G.taps; ++tap) {
+        const int dy = tap / G.ksz, dx = tap - dy * G.ksz;
+        const int cw = w0 * G.stride + dx - G.pad;
+        const int chh = G.flat ? 0 : h0 * G.stride + dy - G.pad;
+        for (int kk = 0; kk < G.kchunks; ++kk, ++kc) {
+          const int s = kc % G.stages;
+          const uint32_t ph = (uint32_t)(kc / G.stages) & 1u;
+          mbar_wait(bar_empty0 + 8u * s, ph ^ 1u);
+          const uint32_t full = bar_full0 + 8u * s;
+          mbar_expect_tx(full, tx);
+          const uint32_t sa = tiles + s * stage_bytes;
+          tma_load_4d(&G.tm_a, full, sa, kk * G.BK, cw, chh, img);
+          tma_load_3d(&G.tm_b, full, sa + a_bytes, kk * G.BK, tap, n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    if (lane == 0) {
+      const uint32_t row_bytes = (uint32_t)G.BK * 2u;
+      const uint32_t sbo = 8u * row_bytes;
+      for (int kc = 0; kc < total_chunks; ++kc) {
+        const int s = kc % G.stages;
+        const uint32_t ph = (uint32_t)(kc / G.stages) & 1u;
+        mbar_wait(bar_full0 + 8u * s, ph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t sa = tiles + s * stage_bytes;
+        const uint64_t da = make_smem_desc(sa, sbo, (uint32_t)G.sw_mode);
+        const uint64_t db = make_smem_desc(sa + a_bytes, sbo, (uint32_t)G.sw_mode);
+        const int nk = G.BK / 16;
+        for (int k = 0; k < nk; ++k) {
+          // advance 16 K-elements = 32 bytes inside the swizzle span: +2 in the (addr >> 4) field
+          umma_bf16(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), G.idesc, (uint32_t)((kc | k) != 0));
+        }
+        umma_commit(bar_empty0 + 8u * s);  // frees the smem stage once these MMAs retire
+      }
+      umma_commit(bar_tmem);               // accumulator complete
+    }
+  } else {
+    // ================================ epilogue ====================================
+    const int q = warp & 3;                 // TMEM lane quarter this warp may read
+    const int row = q * 32 + lane;          // pixel row inside the tile
+    mbar_wait(bar_tmem, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t xr = (uint32_t)(row & 7);
+    const int nchunks = G.BN / 32;
+    for (int cc = 0; cc < nchunks; ++cc) {
+      uint32_t v[32];
+      tmem_ld32(taddr + (uint32_t)(cc * 32), v);
+      float f[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) f[i] = act_fast(__uint_as_float(v[i]) + bias_s[cc * 32 + i], G.act, G.slope);
+      if (G.out_f32) {
+        const uint32_t base = tiles + (uint32_t)cc * 16384u + (uint32_t)row * 128u;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t addr = base + ((((uint32_t)j) ^ xr) << 4);
+          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(f[4 * j]), "f"(f[4 * j + 1]),
+                       "f"(f[4 * j + 2]), "f"(f[4 * j + 3]) : "memory");
+        }
+      } else {
+        const uint32_t base = tiles + (uint32_t)(cc >> 1) * 16384u + (uint32_t)row * 128u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t p[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(f[8 * j + 2 * e], f[8 * j + 2 * e + 1]);
+            p[e] = *reinterpret_cast<uint32_t*>(&h);
+          }
+          const uint32_t addr = base + ((((uint32_t)((cc & 1) * 4 + j)) ^ xr) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(p[0]), "r"(p[1]), "r"(p[2]),
+                       "r"(p[3]) : "memory");
+        }
+      }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to TMA
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (warp == 2 && lane == 0) {
+      const int per_group = G.out_f32 ? 32 : 64;
+      const int ngroups = (G.BN + per_group - 1) / per_group;
+      for (int mp = 0; mp < G.n_store_maps; ++mp)
+        for (int g = 0; g < ngroups; ++g)
+          tma_store_4d(&G.tm_y[mp], tiles + (uint32_t)g * 16384u, n0 + g * per_group, w0, G.flat ? 0 : h0, img);
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G.tmem_cols)
+                 : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+static int encode(CUtensorMap* tm, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
+                  const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr, CUtensorMapSwizzle sw,
+                  const char* what) {
+  EncodeTiledFn fn = get_encode();
+  if (!fn) {
+    set_error("conv(tc): cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+    return YB_ERR_CUDA;
+  }
+  cuuint64_t d[5], st[4];
+  cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = estr[i]; }
+  for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
+  CUresult r = fn(tm, dt, (cuuint32_t)rank, const_cast<void*>(base), d, st, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("conv(tc): cuTensorMapEncodeTiled(%s) failed with %d (dims %llu,%llu,%llu,%llu box %u,%u,%u,%u)", what,
+              (int)r, (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)(rank > 2 ? dims[2] : 0),
+              (unsigned long long)(rank > 3 ? dims[3] : 0), box[0], box[1], rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
+    return YB_ERR_CUDA;
+  }
+  return YB_OK;
+}
+
+struct ConvTcPlan {
+  ConvTcArgs args;
+  int grid;
+  size_t smem;
+};
+
+static int pick_tile_n(int cout) {
+  if (cout <= 32) return 32;
+  int best = 64, best_cost = 1 << 30;
+  const int cands[3] = {64, 128, 256};
+  for (int i = 0; i < 2; ++i) {  // 256 only by explicit override for now
+    int bn = cands[i];
+    int cost = (cout + bn - 1) / bn * bn;
+    if (cost < best_cost || (cost == best_cost && bn > best)) { best = bn; best_cost = cost; }
+  }
+  return best;
+}
+
+int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
+  const yb_tensor& x = d.x;
+  const yb_tensor& y = d.y;
+  YB_CHECK_ARG(x.dtype == YB_BF16, "conv(tc): x must be bf16");
+  YB_CHECK_ARG(y.dtype == YB_BF16 || y.dtype == YB_F32, "conv(tc): y must be bf16 or fp32");
+  YB_CHECK_ARG(d.res.data == nullptr, "conv(tc): fused residual not supported; use yb_add");
+  YB_CHECK_ARG(x.c_stride % 8 == 0 && d.cin_pad % 8 == 0 && (uintptr_t)x.data % 16 == 0 && (uintptr_t)d.weight % 16 == 0,
+               "conv(tc): input channel stride / cin_pad must be multiples of 8 and pointers 16-byte aligned");
+  const int y_es = y.dtype == YB_F32 ? 4 : 2;
+  YB_CHECK_ARG(((size_t)y.c_stride * y_es) % 16 == 0 && (uintptr_t)y.data % 16 == 0,
+               "conv(tc): output channel stride must be a multiple of 16 bytes");
+  const int k = d.k, s = d.stride, pad = k / 2, ups = d.upsample;
+  const int Ho = (x.H + 2 * pad - k) / s + 1, Wo = (x.W + 2 * pad - k) / s + 1;
+  const int Cin = x.C, Cout = y.C;
+  ConvTcPlan* P = new ConvTcPlan();
+  ConvTcArgs& A = P->args;
+  memset(&A, 0, sizeof(A));
+  A.bias = d.bias; A.bias_len = d.cout_pad;
+  A.ksz = k; A.taps = k * k; A.stride = s; A.pad = pad;
+  A.act = d.act; A.slope = d.leaky_slope;
+  A.out_f32 = y.dtype == YB_F32;
+  A.BK = Cin >= 64 ? 64 : (Cin >= 32 ? 32 : 16);
+  if (A.BK > d.cin_pad) A.BK = d.cin_pad >= 32 ? 32 : 16;
+  YB_CHECK_ARG(d.cin_pad >= 16, "conv(tc): cin_pad must be >= 16");
+  A.kchunks = (Cin + A.BK - 1) / A.BK;
+  A.sw_mode = A.BK == 64 ? 2 : (A.BK == 32 ? 4 : 6);
+  const CUtensorMapSwizzle sw_in = A.BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                              : (A.BK == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+  A.BN = d.tile_n ? d.tile_n : pick_tile_n(Cout);
+  YB_CHECK_ARG(A.BN == 32 || A.BN == 64 || A.BN == 128 || A.BN == 256, "conv(tc): tile_n must be 32/64/128/256");
+  A.tiles_n = (Cout + A.BN - 1) / A.BN;
+  A.flat = (k == 1 && s == 1 && ups == 1) ? 1 : 0;
+  int images = x.N;
+  if (A.flat) {
+    const long long M = (long long)x.N * x.H * x.W;
+    A.BW = 128; A.BH = 1;
+    A.tiles_w = (int)((M + 127) / 128); A.tiles_h = 1;
+    images = 1;
+  } else {
+    int best_bw = 1, best_cost = 1 << 30;
+    for (int bw = 1; bw <= 128 && bw <= Wo; ++bw) {
+      int bh = 128 / bw;
+      if (bh > Ho) bh = Ho;
+      if (bh * s > 256 || bw * s > 256) continue;
+      int cost = ((Wo + bw - 1) / bw) * ((Ho + bh - 1) / bh);
+      if (cost < best_cost || (cost == best_cost && bw > best_bw)) { best_cost = cost; best_bw = bw; }
+    }
+    A.BW = best_bw;
+    A.BH = 128 / best_bw < Ho ? 128 / best_bw : Ho;
+    A.tiles_w = (Wo + A.BW - 1) / A.BW;
+    A.tiles_h = (Ho + A.BH - 1) / A.BH;
+  }
+  A.n_store_maps = ups == 2 ? 4 : 1;
+  A.tmem_cols = A.BN < 32 ? 32 : A.BN;
+  A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  // stages / shared memory
+  const size_t stage_bytes = (size_t)128 * A.BK * 2 + (size_t)A.BN * A.BK * 2;
+  const size_t budget = A.BN >= 256 ? 200 * 1024 : 100 * 1024;
+  int stages = d.stages ? d.stages : (int)(budget / stage_bytes);
+  if (stages > 8) stages = 8;
+  if (stages > A.taps * A.kchunks) stages = A.taps * A.kchunks;
+  if (stages < 1) stages = 1;
+  A.stages = stages;
+  size_t pipe = stage_bytes * stages, stage_out = (size_t)128 * A.BN * y_es;
+  if (pipe < stage_out) pipe = stage_out;
+  P->smem = 1024 + pipe + 8 * (2 * stages + 1) + 16 + (size_t)A.BN * 4 + 64;
+  if (P->smem > 227 * 1024) {
+    set_error("conv(tc): shared memory budget exceeded (%zu bytes)", P->smem);
+    delete P;
+    return YB_ERR_INVALID;
+  }
+  int rc;
+  const uint32_t one4[4] = {1, 1, 1, 1};
+  // ---- A: activations
+  {
+    uint64_t dims[4], str[3];
+    uint32_t box[4], es[4] = {1, (uint32_t)s, (uint32_t)s, 1};
+    const uint64_t cs = (uint64_t)x.c_stride * 2;
+    if (A.flat) {
+      const uint64_t M = (uint64_t)x.N * x.H * x.W;
+      dims[0] = Cin; dims[1] = M; dims[2] = 1; dims[3] = 1;
+      str[0] = cs; str[1] = cs * M; str[2] = cs * M;
+      box[0] = A.BK; box[1] = 128; box[2] = 1; box[3] = 1;
+      es[1] = es[2] = 1;
+    } else {
+      dims[0] = Cin; dims[1] = x.W; dims[2] = x.H; dims[3] = x.N;
+      str[0] = cs; str[1] = cs * x.W; str[2] = cs * x.W * x.H;
+      box[0] = A.BK; box[1] = A.BW * s; box[2] = A.BH * s; box[3] = 1;
+    }
+    rc = encode(&A.tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x.data, dims, str, box, es, sw_in, "activations");
+    if (rc) { delete P; return rc; }
+  }
+  // ---- B: weights [cout_pad][taps][cin_pad]
+  {
+    uint64_t dims[3] = {(uint64_t)d.cin_pad, (uint64_t)A.taps, (uint64_t)d.cout_pad};
+    uint64_t str[2] = {(uint64_t)d.cin_pad * 2, (uint64_t)d.cin_pad * 2 * A.taps};
+    uint32_t box[3] = {(uint32_t)A.BK, 1, (uint32_t)A.BN};
+    rc = encode(&A.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, d.weight, dims, str, box, one4, sw_in, "weights");
+    if (rc) { delete P; return rc; }
+  }
+  // ---- Y: outputs (swizzle-128B staging, 128-byte inner box)
+  {
+    const CUtensorMapDataType dt = A.out_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const uint32_t inner = A.out_f32 ? 32 : 64;
+    const uint64_t cs = (uint64_t)y.c_stride * y_es;
+    for (int mp = 0; mp < A.n_store_maps; ++mp) {
+      uint64_t dims[4], str[3];
+      uint32_t box[4] = {inner, (uint32_t)A.BW, (uint32_t)A.BH, 1};
+      const char* base = (const char*)y.data;
+      if (A.flat) {
+        const uint64_t M = (uint64_t)x.N * x.H * x.W;
+        dims[0] = Cout; dims[1] = M; dims[2] = 1; dims[3] = 1;
+        str[0] = cs; str[1] = cs * M; str[2] = cs * M;
+        box[1] = 128; box[2] = 1;
+      } else if (ups == 2) {
+        const int uy = mp >> 1, ux = mp & 1;
+        base += ((size_t)uy * y.W + ux) * cs;
+        dims[0] = Cout; dims[1] = Wo; dims[2] = Ho; dims[3] = x.N;
+        str[0] = 2 * cs; str[1] = 2 * cs * y.W; str[2] = cs * y.W * y.H;
+      } else {
+        dims[0] = Cout; dims[1] = Wo; dims[2] = Ho; dims[3] = x.N;
+        str[0] = cs; str[1] = cs * y.W; str[2] = cs * y.W * y.H;
+      }
+      rc = encode(&A.tm_y[mp], dt, 4, base, dims, str, box, one4, CU_TENSOR_MAP_SWIZZLE_128B, "output");
+      if (rc) { delete P; return rc; }
+    }
+  }
+  YB_CHECK_ARG(y.H == Ho * ups && y.W == Wo * ups && y.N == x.N, "conv(tc): output spatial dims mismatch");
+  const long long grid = (long long)A.tiles_n * A.tiles_w * A.tiles_h * images;
+  YB_CHECK_ARG(grid < 0x7fffffffLL, "conv(tc): grid too large");
+  P->grid = (int)grid;
+  *out = P;
+  return YB_OK;
+}
+
+int conv_tc_launch(const ConvTcPlan* P, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    YB_CUDA(cudaFuncSetAttribute(k_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  k_conv_tc<<<P->grid, kTcThreads, P->smem, s>>>(P->args);
+  YB_LAUNCH_CHECK();
+  return YB_OK;
+}
+
+void conv_tc_plan_destroy(ConvTcPlan* p) { delete p; }
+
+}  // namespace yb
+
+using namespace yb;
+
+extern "C" int yb_conv2d(const yb_conv_desc* d, void* stream) {
+  YB_CHECK_ARG(d && view_ok(d->x) && view_ok(d->y) && d->weight && d->bias, "yb_conv2d: bad descriptor");
+  YB_CHECK_ARG((d->k == 1 || d->k == 3) && (d->stride == 1 || d->stride == 2), "yb_conv2d: k in {1,3}, stride in {1,2}");
+  YB_CHECK_ARG(d->upsample == 1 || d->upsample == 2, "yb_conv2d: upsample must be 1 or 2");
+  YB_CHECK_ARG(d->cin_pad >= d->x.C && d->cout_pad >= d->y.C, "yb_conv2d: padded weight extents too small");
+  const int pad = d->k / 2;
+  const int Ho = (d->x.H + 2 * pad - d->k) / d->stride + 1, Wo = (d->x.W + 2 * pad - d->k) / d->stride + 1;
+  YB_CHECK_ARG(d->y.H == Ho * d->upsample && d->y.W == Wo * d->upsample && d->y.N == d->x.N,
+               "yb_conv2d: output dims must be (%d,%d)", Ho * d->upsample, Wo * d->upsample);
+  if (d->x.dtype == YB_F32) return conv_fp32_launch(*d, (cudaStream_t)stream);
+  ConvTcPlan* p = nullptr;
+  int rc = conv_tc_plan_create(*d, &p);
+  if (rc) return rc;
+  rc = conv_tc_launch(p, (cudaStream_t)stream);
+  conv_tc_plan_destroy(p);
+  return rc;
+}

@@ -1,0 +1,88 @@
+// Detect-head decode: IDetect.fuseforward inference branch (reference models/yolo.py:145-162;
+// exact arithmetic order in SURVEY.md A.5).  Reads the NHWC logits written by the 1x1 head conv
+// once and writes pred (B,A,no) fp32 once (+ optionally the raw (B,na,ny,nx,no) tensors).
+//   p = sigmoid(t); xy = (p*2 - 0.5 + g) * stride; wh = (p*2)^2 * anchor; obj/cls = p
+// Every fp32 step is an explicit round-to-nearest intrinsic so nvcc cannot contract it.
+#include "common.cuh"
+
+namespace yb {
+
+__device__ __forceinline__ float sigmoid_rn(float t) {
+  return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-t)));
+}
+
+__device__ __forceinline__ float decode_elem(float p, int o, int gx, int gy, float stride, float aw, float ah) {
+  if (o >= 4) return p;
+  float p2 = __fmul_rn(p, 2.0f);
+  if (o < 2) {
+    float g = (float)(o == 0 ? gx : gy);
+    return __fmul_rn(__fadd_rn(__fsub_rn(p2, 0.5f), g), stride);
+  }
+  return __fmul_rn(__fmul_rn(p2, p2), o == 2 ? aw : ah);
+}
+
+struct DecodeLevel {
+  const void* logits;
+  int dtype, ny, nx, c_stride;
+  float stride;
+  float anchor_wh[2 * YB_MAX_ANCHORS];
+  int row_off;  // first pred row of this level within an image
+  float* raw;   // nullable
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_decode(DecodeLevel L, int B, int A, int na, int no, float* __restrict__ pred) {
+  const int C = na * no;
+  const size_t total = (size_t)B * L.ny * L.nx * C;
+  const T* in = reinterpret_cast<const T*>(L.logits);
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    int c = (int)(i % C);
+    size_t p = i / C;
+    int x = (int)(p % L.nx);
+    size_t q = p / L.nx;
+    int y = (int)(q % L.ny);
+    int b = (int)(q / L.ny);
+    float t = Elem<T>::load(in + p * L.c_stride + c);
+    int a = c / no, o = c - a * no;
+    float v = decode_elem(sigmoid_rn(t), o, x, y, L.stride, L.anchor_wh[2 * a], L.anchor_wh[2 * a + 1]);
+    size_t cell = ((size_t)a * L.ny + y) * L.nx + x;
+    pred[((size_t)b * A + L.row_off + cell) * no + o] = v;
+    if (L.raw) L.raw[(((size_t)b * na) * L.ny * L.nx + cell) * no + o] = t;
+  }
+}
+
+}  // namespace yb
+
+using namespace yb;
+
+extern "C" int yb_decode(const yb_head_level* levels, int nl, int na, int no, float* pred, float* const* raw,
+                         void* stream) {
+  YB_CHECK_ARG(levels && pred && nl > 0 && nl <= YB_MAX_LEVELS, "yb_decode: bad levels");
+  YB_CHECK_ARG(na > 0 && na <= YB_MAX_ANCHORS && no > 5 - 1, "yb_decode: bad na/no");
+  int A = 0;
+  const int B = levels[0].logits.N;
+  for (int l = 0; l < nl; ++l) {
+    const yb_tensor& t = levels[l].logits;
+    YB_CHECK_ARG(view_ok(t) && t.N == B && t.C >= na * no, "yb_decode: level %d logits view invalid", l);
+    YB_CHECK_ARG(t.dtype == YB_F32 || t.dtype == YB_BF16, "yb_decode: logits must be fp32/bf16");
+    A += na * t.H * t.W;
+  }
+  int off = 0;
+  for (int l = 0; l < nl; ++l) {
+    const yb_tensor& t = levels[l].logits;
+    DecodeLevel L;
+    L.logits = t.data; L.dtype = t.dtype; L.ny = t.H; L.nx = t.W; L.c_stride = t.c_stride;
+    L.stride = levels[l].stride;
+    memcpy(L.anchor_wh, levels[l].anchor_wh, sizeof(L.anchor_wh));
+    L.row_off = off;
+    L.raw = raw ? raw[l] : nullptr;
+    size_t total = (size_t)B * t.H * t.W * na * no;
+    size_t g = (total + 255) / 256, cap = (size_t)num_sms() * 16;
+    int grid = (int)(g < cap ? g : cap);
+    if (t.dtype == YB_F32) k_decode<float><<<grid, 256, 0, (cudaStream_t)stream>>>(L, B, A, na, no, pred);
+    else k_decode<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(L, B, A, na, no, pred);
+    YB_LAUNCH_CHECK();
+    off += na * t.H * t.W;
+  }
+  return YB_OK;
+}

@@ -1,0 +1,538 @@
+// Batched non_max_suppression for B200.
+// Restates reference utils/general.py:628-720 (candidate filter, conf = obj*cls, xywh->xyxy,
+// best-class / multi-label, class whitelist, top-max_nms, 4096-px class offset, max_det) and the
+// greedy suppression of torchvision.ops.nms (call site general.py:704): stable descending sort,
+// iou = inter / (area_i + area_j - inter) in fp32, suppress iff (double)iou > iou_thres, only kept
+// boxes suppress.  Bit-exact by construction: every fp32 step is an explicit *_rn intrinsic.
+//
+// Pipeline (no host sync, no per-image launches):
+//   k_filter    one warp per prediction row; reads the row once, emits 64-bit sort keys
+//               (~score_bits << 32 | row_or_row*nc+cls) by warp-aggregated atomics
+//   k_sort_nms  one CTA per image: LSD radix sort of the keys (stable => ties resolved by original
+//               order, as torch's stable sort does), then chunked greedy NMS against the kept set
+//               held in shared memory, stopping as soon as max_det boxes are kept.
+#include "common.cuh"
+
+namespace yb {
+
+constexpr int kMaxClassWords = 32;  // class whitelist bitmask: nc <= 1024
+constexpr float kMaxWH = 4096.0f;   // general.py:640 max_wh
+
+struct HeadLevelDev {  // fused decode source (yb_decode_nms)
+  const void* logits;
+  int dtype, ny, nx, c_stride;
+  float stride;
+  float anchor_wh[2 * YB_MAX_ANCHORS];
+  int row_off;
+};
+
+struct FilterParams {
+  // source A: decoded predictions (B, A, no) fp32
+  const float* pred;
+  // source B: raw head logits (fused decode)
+  HeadLevelDev lv[YB_MAX_LEVELS];
+  int nl, na;
+  int B, A, no, nc;
+  float conf_thres;
+  int multi_label, use_class_mask;
+  uint32_t class_mask[kMaxClassWords];
+  int cap;
+  // outputs
+  int* count;            // [B]
+  uint64_t* keys;        // [B][cap]
+  uint16_t* cls_of_row;  // [B][A]      (best-class mode)
+  float* boxes;          // [B][A][4]   xywh of candidate rows (fused mode only)
+  int* overflow;         // nullable
+};
+
+__device__ __forceinline__ float sigmoid_rn_(float t) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-t))); }
+
+__device__ __forceinline__ bool class_allowed(const FilterParams& P, int c) {
+  return !P.use_class_mask || ((P.class_mask[c >> 5] >> (c & 31)) & 1u);
+}
+
+// One warp per row.  Lane l holds channels l, l+32, l+64, ... of the row.
+template <bool FUSED, typename TL>
+__global__ void __launch_bounds__(256) k_filter(const FilterParams P) {
+  const int lane = threadIdx.x & 31;
+  const size_t warp0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
+  const size_t nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
+  const size_t rows = (size_t)P.B * P.A;
+  constexpr int MAXV = 8;  // supports no <= 256 per row per warp-iteration chunking below
+  for (size_t r = warp0; r < rows; r += nwarps) {
+    const int b = (int)(r / P.A), row = (int)(r % P.A);
+    // ---- locate the row
+    const float* src = nullptr;
+    const TL* lsrc = nullptr;
+    float stride = 0.f, aw = 0.f, ah = 0.f;
+    int gx = 0, gy = 0;
+    if (!FUSED) {
+      src = P.pred + r * P.no;
+    } else {
+      int l = 0;
+      while (l + 1 < P.nl && row >= P.lv[l + 1].row_off) ++l;
+      const HeadLevelDev& L = P.lv[l];
+      int cell = row - L.row_off;
+      int a = cell / (L.ny * L.nx);
+      int rem = cell - a * L.ny * L.nx;
+      gy = rem / L.nx; gx = rem - gy * L.nx;
+      lsrc = reinterpret_cast<const TL*>(L.logits) + (((size_t)b * L.ny + gy) * L.nx + gx) * L.c_stride + a * P.no;
+      stride = L.stride; aw = L.anchor_wh[2 * a]; ah = L.anchor_wh[2 * a + 1];
+    }
+    // ---- first 32 channels: box + obj (+27 classes)
+    float v0 = 0.f;
+    if (lane < P.no) v0 = FUSED ? sigmoid_rn_(Elem<TL>::load(lsrc + lane)) : __ldg(src + lane);
+    const float obj = __shfl_sync(0xffffffffu, v0, 4);
+    if (!(obj > P.conf_thres)) continue;  // general.py:637,653
+    // xywh (decoded when fused)
+    float bx = __shfl_sync(0xffffffffu, v0, 0), by = __shfl_sync(0xffffffffu, v0, 1);
+    float bw = __shfl_sync(0xffffffffu, v0, 2), bh = __shfl_sync(0xffffffffu, v0, 3);
+    if (FUSED) {
+      bx = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(bx, 2.f), 0.5f), (float)gx), stride);
+      by = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(by, 2.f), 0.5f), (float)gy), stride);
+      float w2 = __fmul_rn(bw, 2.f), h2 = __fmul_rn(bh, 2.f);
+      bw = __fmul_rn(__fmul_rn(w2, w2), aw);
+      bh = __fmul_rn(__fmul_rn(h2, h2), ah);
+    }
+    // ---- class confidences: conf_c = cls_c * obj (general.py:673); nc == 1: conf = obj (:670)
+    float best = -INFINITY;
+    int best_c = 0x7fffffff;
+    int n_emit_total = 0;
+    for (int it = 0; it < MAXV && it * 32 < P.no; ++it) {
+      const int ch = it * 32 + lane;
+      float v = v0;
+      if (it > 0) {
+        v = 0.f;
+        if (ch < P.no) v = FUSED ? sigmoid_rn_(Elem<TL>::load(lsrc + ch)) : __ldg(src + ch);
+      }
+      const int c = ch - 5;
+      const bool is_cls = (c >= 0) && (ch < P.no);
+      float conf = (P.nc == 1) ? obj : __fmul_rn(v, obj);
+      if (!P.multi_label) {
+        if (is_cls && (conf > best)) { best = conf; best_c = c; }  // strict > keeps the first index in-lane
+      } else {
+        const bool emit = is_cls && (conf > P.conf_thres) && class_allowed(P, c);
+        const unsigned m = __ballot_sync(0xffffffffu, emit);
+        if (m) {
+          int base = 0;
+          const int cnt = __popc(m);
+          if (lane == 0) base = atomicAdd(P.count + b, cnt);
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (emit) {
+            const int slot = base + __popc(m & ((1u << lane) - 1u));
+            if (slot < P.cap) {
+              const uint32_t idx = (uint32_t)row * (uint32_t)P.nc + (uint32_t)c;
+              P.keys[(size_t)b * P.cap + slot] = ((uint64_t)(~__float_as_uint(conf)) << 32) | idx;
+            } else if (P.overflow) {
+              *P.overflow = 1;
+            }
+          }
+          n_emit_total += cnt;
+        }
+      }
+    }
+    if (!P.multi_label) {
+      // warp argmax with first-index tie-break (torch.max returns the first maximal index)
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        int oc = __shfl_xor_sync(0xffffffffu, best_c, o);
+        if (ob > best || (ob == best && oc < best_c)) { best = ob; best_c = oc; }
+      }
+      if (lane == 0 && best > P.conf_thres && class_allowed(P, best_c)) {  // general.py:684,688
+        const int slot = atomicAdd(P.count + b, 1);
+        if (slot < P.cap) {
+          P.keys[(size_t)b * P.cap + slot] = ((uint64_t)(~__float_as_uint(best)) << 32) | (uint32_t)row;
+          P.cls_of_row[(size_t)b * P.A + row] = (uint16_t)best_c;
+        } else if (P.overflow) {
+          *P.overflow = 1;
+        }
+        n_emit_total = 1;
+      }
+      n_emit_total = __shfl_sync(0xffffffffu, n_emit_total, 0);
+    }
+    if (FUSED && n_emit_total > 0 && lane == 0) {
+      *reinterpret_cast<float4*>(P.boxes + ((size_t)b * P.A + row) * 4) = make_float4(bx, by, bw, bh);
+    }
+  }
+}
+
+}  // namespace yb
+
+namespace yb {
+
+// ------------------------------------------------------------------------------------------------
+// k_sort_nms: one CTA (1024 threads) per image.
+// ------------------------------------------------------------------------------------------------
+constexpr int kSortThreads = 1024;
+constexpr int kSortWarps = kSortThreads / 32;
+constexpr int kChunk = 256;           // candidates resolved per greedy round
+constexpr int kChunkWords = kChunk / 32;
+
+struct NmsParams {
+  const float* boxsrc;   // xywh rows: pred (stride no) or fused boxes (stride 4)
+  int box_stride;
+  const uint16_t* cls_of_row;
+  const int* count;
+  uint64_t* keys_a;
+  uint64_t* keys_b;
+  int B, A, nc, cap;
+  int multi_label, agnostic;
+  int max_nms, max_det;
+  float thr_f;           // largest float T with (double)T <= iou_thres: (double)iou > thr  <=>  iou > T
+  int thr_nonneg;
+  float* out;            // [B][max_det][6]
+  int* counts_out;       // [B]
+};
+
+__device__ __forceinline__ bool iou_suppresses(float ix1, float iy1, float ix2, float iy2, float iarea,
+                                               float jx1, float jy1, float jx2, float jy2, float jarea,
+                                               float thr_f, int thr_nonneg) {
+  const float w = fmaxf(0.0f, __fsub_rn(fminf(ix2, jx2), fmaxf(ix1, jx1)));
+  const float h = fmaxf(0.0f, __fsub_rn(fminf(iy2, jy2), fmaxf(iy1, jy1)));
+  const float inter = __fmul_rn(w, h);
+  if (thr_nonneg && inter == 0.0f) return false;  // iou is 0 or NaN: never > T when T >= 0
+  const float ovr = __fdiv_rn(inter, __fsub_rn(__fadd_rn(iarea, jarea), inter));
+  return ovr > thr_f;
+}
+
+__global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int b = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int n = P.count[b];
+  if (n > P.cap) n = P.cap;
+  uint64_t* src = P.keys_a + (size_t)b * P.cap;
+  uint64_t* dst = P.keys_b + (size_t)b * P.cap;
+
+  // =============================== stable LSD radix sort (8-bit digits) ========================
+  {
+    int* whist = reinterpret_cast<int*>(smem_raw);            // [kSortWarps][256]
+    __shared__ unsigned long long s_and, s_or;
+    if (tid == 0) { s_and = ~0ull; s_or = 0ull; }
+    __syncthreads();
+    unsigned long long a = ~0ull, o = 0ull;
+    for (int i = tid; i < n; i += kSortThreads) { unsigned long long k = src[i]; a &= k; o |= k; }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+      a &= __shfl_xor_sync(0xffffffffu, a, s);
+      o |= __shfl_xor_sync(0xffffffffu, o, s);
+    }
+    if (lane == 0) { atomicAnd(&s_and, a); atomicOr(&s_or, o); }
+    __syncthreads();
+    const unsigned long long varying = s_and ^ s_or;
+    // contiguous segment of the array owned by each warp (keeps the scatter stable)
+    const int per_warp = ((n + kSortWarps - 1) / kSortWarps + 31) / 32 * 32;
+    const int seg0 = min(n, warp * per_warp), seg1 = min(n, seg0 + per_warp);
+    for (int pass = 0; pass < 8 && n > 1; ++pass) {
+      const int sh = pass * 8;
+      if (((varying >> sh) & 0xffull) == 0) continue;  // digit identical for every key
+      for (int i = tid; i < kSortWarps * 256; i += kSortThreads) whist[i] = 0;
+      __syncthreads();
+      int* myh = whist + warp * 256;
+      for (int i = seg0 + lane; i - lane < seg1; i += 32) {
+        const bool valid = i < seg1;
+        const int d = valid ? (int)((src[i] >> sh) & 0xff) : 256 + lane;  // unique dummy digit per idle lane
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        if (valid && lane == __ffs(peers) - 1) myh[d] += __popc(peers);
+        __syncwarp();
+      }
+      __syncthreads();
+      // exclusive scan in (digit major, warp minor) order: thread t<256 owns digit t
+      __shared__ int digit_tot[256];
+      if (tid < 256) {
+        int s = 0;
+        for (int w = 0; w < kSortWarps; ++w) { int c = whist[w * 256 + tid]; whist[w * 256 + tid] = s; s += c; }
+        digit_tot[tid] = s;
+      }
+      __syncthreads();
+      if (warp == 0) {  // scan the 256 digit totals
+        int carry = 0;
+        for (int base = 0; base < 256; base += 32) {
+          int v = digit_tot[base + lane], x = v;
+#pragma unroll
+          for (int s = 1; s < 32; s <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, s); if (lane >= s) x += y; }
+          digit_tot[base + lane] = carry + x - v;
+          carry += __shfl_sync(0xffffffffu, x, 31);
+        }
+      }
+      __syncthreads();
+      if (tid < 256) {
+        const int base = digit_tot[tid];
+        for (int w = 0; w < kSortWarps; ++w) whist[w * 256 + tid] += base;
+      }
+      __syncthreads();
+      for (int i = seg0 + lane; i - lane < seg1; i += 32) {
+        const bool valid = i < seg1;
+        unsigned long long k = valid ? src[i] : 0ull;
+        const int d = valid ? (int)((k >> sh) & 0xff) : 256 + lane;
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        int pos = 0;
+        if (valid) pos = myh[d] + __popc(peers & ((1u << lane) - 1u));
+        __syncwarp();
+        if (valid && lane == __ffs(peers) - 1) myh[d] += __popc(peers);
+        __syncwarp();
+        if (valid) dst[pos] = k;
+      }
+      __syncthreads();
+      uint64_t* t = src; src = dst; dst = t;
+    }
+  }
+  __syncthreads();
+
+  // =============================== greedy NMS ================================================
+  const int m = min(n, P.max_nms);  // general.py:698-699
+  float* kx1 = reinterpret_cast<float*>(smem_raw);
+  float* ky1 = kx1 + P.max_det;
+  float* kx2 = ky1 + P.max_det;
+  float* ky2 = kx2 + P.max_det;
+  float* kar = ky2 + P.max_det;
+  float* cx1 = kar + P.max_det;  // chunk (offset boxes)
+  float* cy1 = cx1 + kChunk;
+  float* cx2 = cy1 + kChunk;
+  float* cy2 = cx2 + kChunk;
+  float* car = cy2 + kChunk;
+  float* craw = car + kChunk;    // [kChunk][4] un-offset xyxy
+  float* cconf = craw + 4 * kChunk;
+  float* ccls = cconf + kChunk;
+  uint32_t* cmask = reinterpret_cast<uint32_t*>(ccls + kChunk);  // [kChunk][kChunkWords]
+  unsigned char* calive = reinterpret_cast<unsigned char*>(cmask + kChunk * kChunkWords);
+  __shared__ uint32_t s_alive[kChunkWords], s_new[kChunkWords];
+  __shared__ int s_K;
+  if (tid == 0) s_K = 0;
+  __syncthreads();
+
+  for (int base = 0; base < m; base += kChunk) {
+    const int K = s_K;
+    if (K >= P.max_det) break;
+    const int cnt = min(kChunk, m - base);
+    // ---- load chunk: un-offset xyxy, class offset, offset boxes + area (general.py:676,702-703)
+    if (tid < cnt) {
+      const unsigned long long key = src[base + tid];
+      const uint32_t idx = (uint32_t)key;
+      const float conf = __uint_as_float(~(uint32_t)(key >> 32));
+      int row, cls;
+      if (P.multi_label) { row = (int)(idx / (uint32_t)P.nc); cls = (int)(idx - (uint32_t)row * P.nc); }
+      else { row = (int)idx; cls = P.cls_of_row[(size_t)b * P.A + row]; }
+      const float* bp = P.boxsrc + ((size_t)b * P.A + row) * P.box_stride;
+      const float x = bp[0], y = bp[1], hw = __fmul_rn(bp[2], 0.5f), hh = __fmul_rn(bp[3], 0.5f);  // w/2 exact
+      const float x1 = __fsub_rn(x, hw), y1 = __fsub_rn(y, hh), x2 = __fadd_rn(x, hw), y2 = __fadd_rn(y, hh);
+      const float c = P.agnostic ? 0.0f : __fmul_rn((float)cls, kMaxWH);
+      const float ox1 = __fadd_rn(x1, c), oy1 = __fadd_rn(y1, c), ox2 = __fadd_rn(x2, c), oy2 = __fadd_rn(y2, c);
+      cx1[tid] = ox1; cy1[tid] = oy1; cx2[tid] = ox2; cy2[tid] = oy2;
+      car[tid] = __fmul_rn(__fsub_rn(ox2, ox1), __fsub_rn(oy2, oy1));
+      craw[4 * tid + 0] = x1; craw[4 * tid + 1] = y1; craw[4 * tid + 2] = x2; craw[4 * tid + 3] = y2;
+      cconf[tid] = conf; ccls[tid] = (float)cls;
+    }
+    __syncthreads();
+    // ---- phase A: candidate j vs every kept box (4 threads per candidate)
+    {
+      const int j = tid >> 2, part = tid & 3;
+      bool sup = false;
+      if (j < cnt) {
+        const float jx1 = cx1[j], jy1 = cy1[j], jx2 = cx2[j], jy2 = cy2[j], ja = car[j];
+        for (int k = part; k < K && !sup; k += 4)
+          sup = iou_suppresses(kx1[k], ky1[k], kx2[k], ky2[k], kar[k], jx1, jy1, jx2, jy2, ja, P.thr_f, P.thr_nonneg);
+      }
+      unsigned s = sup ? 1u : 0u;
+      s |= __shfl_xor_sync(0xffffffffu, s, 1);
+      s |= __shfl_xor_sync(0xffffffffu, s, 2);
+      if (part == 0) calive[j] = (j < cnt && !s) ? 1 : 0;
+    }
+    __syncthreads();
+    if (tid < kChunkWords) {
+      uint32_t w = 0;
+      for (int q = 0; q < 32; ++q) w |= (uint32_t)calive[tid * 32 + q] << q;
+      s_alive[tid] = w;
+      s_new[tid] = 0;
+    }
+    // ---- phase B: intra-chunk suppression bit matrix, rows of live candidates only
+    {
+      const int i = tid >> 2, part = tid & 3;
+      if (i < cnt && calive[i]) {
+        const float ix1 = cx1[i], iy1 = cy1[i], ix2 = cx2[i], iy2 = cy2[i], ia = car[i];
+        for (int w = part; w < kChunkWords; w += 4) {
+          uint32_t word = 0;
+          const int j0 = w * 32;
+          if (j0 + 31 > i) {
+            for (int q = 0; q < 32; ++q) {
+              const int j = j0 + q;
+              if (j > i && j < cnt && calive[j] &&
+                  iou_suppresses(ix1, iy1, ix2, iy2, ia, cx1[j], cy1[j], cx2[j], cy2[j], car[j], P.thr_f, P.thr_nonneg))
+                word |= 1u << q;
+            }
+          }
+          cmask[i * kChunkWords + w] = word;
+        }
+      }
+    }
+    __syncthreads();
+    // ---- phase C: serial resolve over live candidates (one thread; cost ~ number kept)
+    if (tid == 0) {
+      uint32_t removed[kChunkWords];
+#pragma unroll
+      for (int w = 0; w < kChunkWords; ++w) removed[w] = 0;
+      int Kc = K;
+#pragma unroll 1
+      for (int w = 0; w < kChunkWords && Kc < P.max_det; ++w) {
+        uint32_t bits = s_alive[w] & ~removed[w];
+        while (bits && Kc < P.max_det) {
+          const int q = __ffs(bits) - 1;
+          const int i = w * 32 + q;
+          s_new[w] |= 1u << q;
+          ++Kc;
+#pragma unroll
+          for (int ww = 0; ww < kChunkWords; ++ww) removed[ww] |= cmask[i * kChunkWords + ww];
+          bits = s_alive[w] & ~removed[w] & ~((2u << q) - 1u);
+        }
+      }
+      s_K = Kc;
+    }
+    __syncthreads();
+    // ---- phase D: append the newly kept boxes to the kept set and write output rows
+    if (tid < cnt && ((s_new[tid >> 5] >> (tid & 31)) & 1u)) {
+      int pos = K + __popc(s_new[tid >> 5] & ((1u << (tid & 31)) - 1u));
+      for (int w = 0; w < (tid >> 5); ++w) pos += __popc(s_new[w]);
+      kx1[pos] = cx1[tid]; ky1[pos] = cy1[tid]; kx2[pos] = cx2[tid]; ky2[pos] = cy2[tid]; kar[pos] = car[tid];
+      float* o = P.out + ((size_t)b * P.max_det + pos) * 6;
+      o[0] = craw[4 * tid + 0]; o[1] = craw[4 * tid + 1]; o[2] = craw[4 * tid + 2]; o[3] = craw[4 * tid + 3];
+      o[4] = cconf[tid]; o[5] = ccls[tid];
+    }
+    __syncthreads();
+  }
+  if (tid == 0) P.counts_out[b] = s_K;
+}
+
+// ------------------------------------------------------------------------------------------------
+struct NmsWorkspace {
+  int* count; uint64_t* keys_a; uint64_t* keys_b; uint16_t* cls_of_row; float* boxes;
+  size_t total;
+};
+
+static NmsWorkspace carve(void* ws, int B, int A, int cap, bool fused) {
+  NmsWorkspace w;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+  char* p = (char*)ws;
+  w.count = (int*)(p + take((size_t)B * 4));
+  w.keys_a = (uint64_t*)(p + take((size_t)B * cap * 8));
+  w.keys_b = (uint64_t*)(p + take((size_t)B * cap * 8));
+  w.cls_of_row = (uint16_t*)(p + take((size_t)B * A * 2));
+  w.boxes = (float*)(p + take(fused ? (size_t)B * A * 16 : 0));
+  w.total = off;
+  return w;
+}
+
+static int resolve_cap(int A, int nc, int multi_label, int cand_cap) {
+  long long full = multi_label ? (long long)A * nc : A;
+  if (cand_cap > 0 && cand_cap < full) return cand_cap;
+  return (int)(full > 0x7fffffffLL ? 0x7fffffff : full);
+}
+
+static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_thres, int agnostic, int max_nms,
+                      int max_det, const int* classes, int n_classes, void* workspace, size_t workspace_bytes,
+                      float* out, int* counts, int* overflow, cudaStream_t s) {
+  const int B = F.B, A = F.A;
+  YB_CHECK_ARG(B > 0 && A > 0 && F.no > 5, "nms: need no >= 6 (nc >= 1)");
+  YB_CHECK_ARG(F.no <= 256, "nms: no > 256 unsupported");
+  YB_CHECK_ARG(max_det > 0 && max_det <= 4096, "nms: max_det must be in [1,4096]");
+  YB_CHECK_ARG(max_nms > 0, "nms: max_nms must be positive");
+  YB_CHECK_ARG(out && counts && workspace, "nms: null output/workspace");
+  YB_CHECK_ARG((long long)A * F.nc < 0xffffffffLL, "nms: A*nc must fit 32 bits");
+  F.use_class_mask = 0;
+  memset(F.class_mask, 0, sizeof(F.class_mask));
+  if (classes) {  // general.py:687-688 (an empty list filters everything, like tensor([]) any() == False)
+    F.use_class_mask = 1;
+    for (int i = 0; i < n_classes; ++i) {
+      if (classes[i] >= 0 && classes[i] < kMaxClassWords * 32) F.class_mask[classes[i] >> 5] |= 1u << (classes[i] & 31);
+    }
+  }
+  NmsWorkspace W = carve(workspace, B, A, F.cap, fused);
+  YB_CHECK_ARG((uintptr_t)workspace % 256 == 0, "nms: workspace must be 256-byte aligned");
+  if (W.total > workspace_bytes) {
+    set_error("nms: workspace too small (%zu < %zu)", workspace_bytes, W.total);
+    return YB_ERR_WORKSPACE;
+  }
+  F.count = W.count; F.keys = W.keys_a; F.cls_of_row = W.cls_of_row; F.boxes = W.boxes; F.overflow = overflow;
+  YB_CUDA(cudaMemsetAsync(W.count, 0, (size_t)B * 4, s));
+  if (overflow) YB_CUDA(cudaMemsetAsync(overflow, 0, 4, s));
+  {
+    size_t rows = (size_t)B * A;
+    size_t g = (rows + 7) / 8, cap = (size_t)num_sms() * 8;
+    int grid = (int)(g < cap ? g : cap);
+    if (!fused) k_filter<false, float><<<grid, 256, 0, s>>>(F);
+    else if (logits_dtype == YB_F32) k_filter<true, float><<<grid, 256, 0, s>>>(F);
+    else k_filter<true, __nv_bfloat16><<<grid, 256, 0, s>>>(F);
+    YB_LAUNCH_CHECK();
+  }
+  NmsParams N;
+  N.boxsrc = fused ? W.boxes : F.pred;
+  N.box_stride = fused ? 4 : F.no;
+  N.cls_of_row = W.cls_of_row; N.count = W.count; N.keys_a = W.keys_a; N.keys_b = W.keys_b;
+  N.B = B; N.A = A; N.nc = F.nc; N.cap = F.cap; N.multi_label = F.multi_label; N.agnostic = agnostic;
+  N.max_nms = max_nms; N.max_det = max_det;
+  float T = (float)iou_thres;  // largest float with (double)T <= iou_thres
+  if ((double)T > iou_thres) T = nextafterf(T, -INFINITY);
+  N.thr_f = T; N.thr_nonneg = (T >= 0.0f) ? 1 : 0;
+  N.out = out; N.counts_out = counts;
+  size_t sm_sort = (size_t)kSortWarps * 256 * 4;
+  size_t sm_nms = (size_t)max_det * 5 * 4 + (size_t)kChunk * (5 + 4 + 2) * 4 + (size_t)kChunk * kChunkWords * 4 + kChunk;
+  size_t smem = sm_sort > sm_nms ? sm_sort : sm_nms;
+  YB_CUDA(cudaFuncSetAttribute(k_sort_nms, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_sort_nms<<<B, kSortThreads, smem, s>>>(N);
+  YB_LAUNCH_CHECK();
+  return YB_OK;
+}
+
+}  // namespace yb
+
+using namespace yb;
+
+extern "C" size_t yb_nms_workspace_bytes(int B, int A, int no, int multi_label, int cand_cap) {
+  if (B <= 0 || A <= 0 || no <= 5) return 0;
+  multi_label = multi_label && (no - 5 > 1);
+  int cap = resolve_cap(A, no - 5, multi_label, cand_cap);
+  return carve(nullptr, B, A, cap, true).total;
+}
+
+extern "C" int yb_nms(const float* pred, int B, int A, int no, float conf_thres, double iou_thres,
+                      const int* classes, int n_classes, int agnostic, int multi_label, int max_nms, int max_det,
+                      int cand_cap, void* workspace, size_t workspace_bytes, float* out, int* counts,
+                      int* overflow, void* stream) {
+  YB_CHECK_ARG(pred, "yb_nms: null pred");
+  FilterParams F;
+  memset(&F, 0, sizeof(F));
+  F.pred = pred; F.B = B; F.A = A; F.no = no; F.nc = no - 5; F.conf_thres = conf_thres;
+  F.multi_label = (multi_label && F.nc > 1) ? 1 : 0;  // general.py:645
+  F.cap = resolve_cap(A, F.nc, F.multi_label, cand_cap);
+  return nms_common(F, false, YB_F32, iou_thres, agnostic, max_nms, max_det, classes, n_classes, workspace,
+                    workspace_bytes, out, counts, overflow, (cudaStream_t)stream);
+}
+
+extern "C" int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no, float conf_thres,
+                             double iou_thres, const int* classes, int n_classes, int agnostic, int multi_label,
+                             int max_nms, int max_det, int cand_cap, void* workspace, size_t workspace_bytes,
+                             float* out, int* counts, int* overflow, void* stream) {
+  YB_CHECK_ARG(levels && nl > 0 && nl <= YB_MAX_LEVELS && na > 0 && na <= YB_MAX_ANCHORS, "yb_decode_nms: bad levels");
+  FilterParams F;
+  memset(&F, 0, sizeof(F));
+  int A = 0;
+  const int B = levels[0].logits.N;
+  const int dt = levels[0].logits.dtype;
+  for (int l = 0; l < nl; ++l) {
+    const yb_tensor& t = levels[l].logits;
+    YB_CHECK_ARG(view_ok(t) && t.N == B && t.C >= na * no && t.dtype == dt, "yb_decode_nms: level %d invalid", l);
+    YB_CHECK_ARG(dt == YB_F32 || dt == YB_BF16, "yb_decode_nms: logits must be fp32/bf16");
+    HeadLevelDev& L = F.lv[l];
+    L.logits = t.data; L.dtype = t.dtype; L.ny = t.H; L.nx = t.W; L.c_stride = t.c_stride;
+    L.stride = levels[l].stride;
+    memcpy(L.anchor_wh, levels[l].anchor_wh, sizeof(L.anchor_wh));
+    L.row_off = A;
+    A += na * t.H * t.W;
+  }
+  F.nl = nl; F.na = na; F.B = B; F.A = A; F.no = no; F.nc = no - 5; F.conf_thres = conf_thres;
+  F.multi_label = (multi_label && F.nc > 1) ? 1 : 0;
+  F.cap = resolve_cap(A, F.nc, F.multi_label, cand_cap);
+  return nms_common(F, true, dt, iou_thres, agnostic, max_nms, max_det, classes, n_classes, workspace,
+                    workspace_bytes, out, counts, overflow, (cudaStream_t)stream);
+}
