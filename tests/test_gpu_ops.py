@@ -1,0 +1,119 @@
+"""GPU parity of the trunk operators vs plain PyTorch fp32 references of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _nhwc(x):
+    return x.permute(0, 2, 3, 1).contiguous()
+
+
+def _nchw(x):
+    return x.permute(0, 3, 1, 2).contiguous()
+
+
+def _ref_conv(x_nchw, w, b, s, act, slope, ups):
+    y = F.conv2d(x_nchw, w, b, s, w.shape[-1] // 2)
+    if act == 1:
+        y = F.silu(y)
+    elif act == 2:
+        y = F.leaky_relu(y, slope)
+    if ups == 2:
+        y = F.interpolate(y, scale_factor=2, mode='nearest')
+    return y
+
+
+CONV_CASES = [
+    # (N, H, W, Cin, Cout, k, s, act, ups)
+    (2, 20, 20, 64, 64, 1, 1, 1, 1),
+    (2, 20, 20, 128, 256, 3, 1, 1, 1),
+    (1, 40, 40, 256, 128, 1, 1, 1, 2),      # lateral conv + fused upsample
+    (2, 24, 40, 64, 128, 3, 2, 1, 1),       # stride 2
+    (1, 64, 96, 16, 32, 3, 1, 1, 1),        # stem-like (Cin padded to 16, SW32)
+    (1, 64, 64, 32, 64, 3, 2, 2, 1),        # Cin 32 (SW64), LeakyReLU
+    (2, 20, 20, 80, 160, 3, 1, 1, 1),       # e6e widths: Cin not a multiple of 64
+    (1, 20, 20, 512, 255, 1, 1, 0, 1),      # head conv (Cout 255)
+    (1, 160, 160, 64, 64, 3, 1, 1, 1),      # wide map, many tiles
+    (3, 12, 20, 96, 96, 3, 1, 1, 1),        # ragged tiles
+]
+
+
+@pytest.mark.parametrize('case', CONV_CASES, ids=[str(c) for c in CONV_CASES])
+def test_conv_fp32_reference_mode(case):
+    from yolo_series_b200 import ops
+    N, H, W, Ci, Co, k, s, act, ups = case
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn((N, Ci, H, W), generator=g)
+    w = torch.randn((Co, Ci, k, k), generator=g) / (Ci * k * k) ** 0.5
+    b = torch.randn((Co,), generator=g)
+    ref = _ref_conv(x, w, b, s, act, 0.1, ups)
+    y = ops.conv2d(_nhwc(x).cuda(), w, b, s, act, 0.1, ups)
+    got = _nchw(y[..., :Co].float().cpu())
+    assert torch.allclose(got, ref, rtol=1e-4, atol=1e-4), float((got - ref).abs().max())
+
+
+@pytest.mark.parametrize('case', CONV_CASES, ids=[str(c) for c in CONV_CASES])
+def test_conv_tcgen05_bf16(case):
+    """bf16 operands, fp32 accumulate: compare against an fp32 conv of the bf16-rounded operands.
+    Tolerance: output rounding to bf16 (2^-8 relative) + accumulation-order noise."""
+    from yolo_series_b200 import ops
+    N, H, W, Ci, Co, k, s, act, ups = case
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn((N, Ci, H, W), generator=g).bfloat16().float()
+    w = (torch.randn((Co, Ci, k, k), generator=g) / (Ci * k * k) ** 0.5).bfloat16().float()
+    b = torch.randn((Co,), generator=g)
+    ref = _ref_conv(x, w, b, s, act, 0.1, ups)
+    head = Co == 255
+    y = ops.conv2d(_nhwc(x).cuda().bfloat16(), w, b, s, act, 0.1, ups, out_dtype=torch.float32 if head else None)
+    got = _nchw(y[..., :Co].float().cpu())
+    tol = 2e-3 if head else 1.2e-2
+    assert torch.allclose(got, ref, rtol=tol, atol=tol), float((got - ref).abs().max())
+
+
+def test_conv_tc_writes_concat_slice():
+    from yolo_series_b200 import ops
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn((1, 64, 16, 16), generator=g).bfloat16().float()
+    w = (torch.randn((64, 64, 3, 3), generator=g) / 24).bfloat16().float()
+    b = torch.zeros(64)
+    out = torch.full((1, 16, 16, 256), 7.0, dtype=torch.bfloat16, device='cuda')
+    ops.conv2d(_nhwc(x).cuda().bfloat16(), w, b, 1, 0, 0.0, 1, out=out, out_c_off=128)
+    ref = F.conv2d(x, w, b, 1, 1)
+    o = out.float().cpu()
+    assert torch.all(o[..., :128] == 7.0) and torch.all(o[..., 192:] == 7.0)
+    assert torch.allclose(_nchw(o[..., 128:192]), ref, rtol=1.2e-2, atol=1.2e-2)
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_pools_upsample_add(dtype):
+    from yolo_series_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn((2, 64, 20, 28), generator=g).to(dtype)
+    xc = _nhwc(x).cuda()
+    xf = x.float()
+    assert torch.equal(_nchw(ops.maxpool2x2(xc).float().cpu()), F.max_pool2d(xf, 2, 2))
+    for k in (5, 9, 13):
+        assert torch.equal(_nchw(ops.maxpool_s1(xc, k).float().cpu()), F.max_pool2d(xf, k, 1, k // 2))
+    s3 = _nchw(ops.spp3(xc).float().cpu())
+    for i, k in enumerate((5, 9, 13)):
+        assert torch.equal(s3[:, i * 64:(i + 1) * 64], F.max_pool2d(xf, k, 1, k // 2))
+    assert torch.equal(_nchw(ops.upsample2x(xc).float().cpu()), F.interpolate(xf, scale_factor=2, mode='nearest'))
+    y = torch.randn((2, 64, 20, 28), generator=g).to(dtype)
+    assert torch.equal(_nchw(ops.add(xc, _nhwc(y).cuda()).cpu()).float(), (x + y).float())
+
+
+def test_stage_input_and_reorg():
+    from yolo_series_b200 import ops
+    g = torch.Generator().manual_seed(4)
+    u8 = torch.randint(0, 256, (2, 3, 32, 48), generator=g, dtype=torch.uint8)
+    ref = u8.float() / 255.0
+    y = ops.stage_input(u8.cuda(), 4, torch.float32)
+    assert torch.equal(_nchw(y.cpu())[:, :3], ref) and torch.all(y[..., 3] == 0)
+    yb = ops.stage_input(ref.cuda(), 16, torch.bfloat16)
+    assert torch.equal(_nchw(yb.float().cpu())[:, :3], ref.bfloat16().float())
+    r = ops.stage_input(ref.cuda(), 16, torch.float32, reorg=True)
+    a = ref
+    want = torch.cat([a[..., ::2, ::2], a[..., 1::2, ::2], a[..., ::2, 1::2], a[..., 1::2, 1::2]], 1)
+    assert torch.equal(_nchw(r.cpu())[:, :12], want) and torch.all(r[..., 12:] == 0)

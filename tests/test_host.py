@@ -1,0 +1,141 @@
+"""CPU-side checks: cfg parser / module mirror / folding / lowering / C-ABI surface."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle.ref_forward import ref_forward
+from oracle.synth import seeded_state_dict, synth_image
+from yolo_series_b200 import Model, _lib, fold, plan, zoo
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, 'include', 'yolo_b200.h')).read()
+    declared = set(re.findall(r'\b(yb_[a-z0-9_]+)\s*\(', hdr))
+    assert declared == set(_lib.EXPORTS), declared ^ set(_lib.EXPORTS)
+    L = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert _lib.lib().yb_abi_version() == 1
+    assert _lib.lib().yb_nms_workspace_bytes(2, 1000, 85, 0, 0) > 2 * 1000 * 16
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, 'yolo_series_b200')
+    for fn in os.listdir(pkg):
+        if fn.endswith('.py'):
+            src = open(os.path.join(pkg, fn)).read()
+            assert 'import oracle' not in src and 'from oracle' not in src, fn
+
+
+def test_model_surface_and_strides():
+    m = Model('yolov7')
+    assert m.stride.tolist() == [8., 16., 32.] and len(m.model) == 106
+    h = m.model[-1]
+    assert (h.nl, h.na, h.nc, h.no) == (3, 3, 80, 85)
+    assert torch.allclose(h.anchors[0] * 8, h.anchor_grid[0].view(3, 2))
+    assert next(m.parameters()).dtype == torch.float32
+    w6 = Model('yolov7-w6-custom')
+    assert w6.stride.tolist() == [8., 16., 32., 64.] and w6.model[-1].no == 88
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(1, 3, 64, 64))       # no CPU fallback
+
+
+def test_lowering_statistics():
+    from collections import Counter
+    want = {'yolov7': (92, 5, 1, 0), 'yolov7-tiny': (58, 3, 1, 0), 'yolov7-w6-custom': (107, 0, 1, 0),
+            'yolov7-e6e': (244, 8, 1, 11)}
+    for name, (nconv, nmp, nspp, nadd) in want.items():
+        L = plan.lower(Model(name).model, 3)
+        c = Counter(o.kind for o in L.ops)
+        assert (c[_lib.OP_CONV], c[_lib.OP_MAXPOOL2], c[_lib.OP_SPP3], c[_lib.OP_ADD]) == (nconv, nmp, nspp, nadd)
+        assert c[_lib.OP_COPY] == 0 and c[_lib.OP_UPSAMPLE2] == 0     # concat + upsample fully planned away
+
+
+def _run_lowered_cpu(L, x):
+    """Interpret the lowered op list with torch CPU ops (test-only) to validate fold + placement logic."""
+    vals = {}
+
+    def root(v):
+        off = 0
+        while L.vals[v].parent is not None:
+            off += L.vals[v].offset
+            v = L.vals[v].parent
+        return v, off
+    bufs = {}
+
+    def read(v):
+        r, off = root(v)
+        return bufs[r][:, off:off + L.vals[v].C]
+
+    def write(v, t):
+        r, off = root(v)
+        if r not in bufs:
+            bufs[r] = torch.zeros((t.shape[0], L.vals[r].C, t.shape[2], t.shape[3]))
+        bufs[r][:, off:off + L.vals[v].C] = t
+    if L.reorg:
+        x = torch.cat([x[..., ::2, ::2], x[..., 1::2, ::2], x[..., ::2, 1::2], x[..., 1::2, 1::2]], 1)
+    bufs[L.input_val] = x
+    for op in L.ops:
+        a = read(op.ins[0])
+        if op.kind == _lib.OP_CONV:
+            fc = op.conv
+            y = F.conv2d(a, fc.weight, fc.bias, fc.s, fc.k // 2)
+            y = F.silu(y) if fc.act == 1 else (F.leaky_relu(y, fc.slope) if fc.act == 2 else y)
+            if op.upsample == 2:
+                y = F.interpolate(y, scale_factor=2, mode='nearest')
+            write(op.outs[0], y)
+        elif op.kind == _lib.OP_MAXPOOL2:
+            write(op.outs[0], F.max_pool2d(a, 2, 2))
+        elif op.kind == _lib.OP_SPP3:
+            for o, k in zip(op.outs, (5, 9, 13)):
+                write(o, F.max_pool2d(a, k, 1, k // 2))
+        elif op.kind == _lib.OP_POOL_S1:
+            write(op.outs[0], F.max_pool2d(a, op.k, 1, op.k // 2))
+        elif op.kind == _lib.OP_ADD:
+            write(op.outs[0], a + read(op.ins[1]))
+        elif op.kind == _lib.OP_COPY:
+            write(op.outs[0], a)
+        elif op.kind == _lib.OP_UPSAMPLE2:
+            write(op.outs[0], F.interpolate(a, scale_factor=2, mode='nearest'))
+    return [read(v) for v in L.head_vals]
+
+
+@pytest.mark.parametrize('name,hw', [('yolov7-tiny', 64), ('yolov7', 64), ('yolov7-e6e', 128)])
+def test_fold_and_placement_reproduce_oracle_logits(name, hw):
+    """The lowered graph (folded weights, concat placement, fused upsample, dead aux removal) computes the
+    same head logits as the oracle's node-by-node forward."""
+    m = Model(name)
+    sd = seeded_state_dict(m, seed=0)
+    m.load_state_dict(sd)
+    x = synth_image(1, hw, hw, seed=3)
+    with torch.no_grad():
+        L = plan.lower(m.model, 3)
+        heads = _run_lowered_cpu(L, x)
+        _, raws = ref_forward(zoo.get_cfg(name), sd, x, fused=True)
+    for h, r in zip(heads, raws):
+        b, na, ny, nx, no = r.shape
+        got = h.view(b, na, no, ny, nx).permute(0, 1, 3, 4, 2)
+        assert torch.allclose(got, r, rtol=1e-4, atol=1e-4), float((got - r).abs().max())
+
+
+def test_repconv_identity_branch_fold():
+    from yolo_series_b200.modules import RepConv
+    torch.manual_seed(0)
+    m = RepConv(16, 16, 3, 1)
+    for bn in (m.rbr_identity, m.rbr_dense[1], m.rbr_1x1[1]):
+        bn.running_mean.normal_(0, 0.2); bn.running_var.uniform_(0.5, 1.5); bn.weight.data.uniform_(0.5, 1.5); bn.bias.data.normal_()
+        bn.eps = 1e-3
+    x = torch.randn(1, 16, 8, 8)
+    with torch.no_grad():
+        def bnf(bn, t): return F.batch_norm(t, bn.running_mean, bn.running_var, bn.weight, bn.bias, False, 0., bn.eps)
+        ref = F.silu(bnf(m.rbr_dense[1], F.conv2d(x, m.rbr_dense[0].weight, None, 1, 1)) +
+                     bnf(m.rbr_1x1[1], F.conv2d(x, m.rbr_1x1[0].weight, None, 1, 0)) + bnf(m.rbr_identity, x))
+        fc = fold.fold_repconv(m)
+        got = F.silu(F.conv2d(x, fc.weight, fc.bias, 1, 1))
+    assert torch.allclose(got, ref, atol=1e-5)

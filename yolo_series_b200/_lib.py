@@ -1,0 +1,112 @@
+"""ctypes binding of libyolo_b200.so (C ABI declared in include/yolo_b200.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` / ``make -C yolo_series_b200/csrc``.
+There is NO fallback: if the shared object is missing, loading raises, and every compute entry
+point raises ``RuntimeError`` with ``yb_last_error()`` on a non-zero status.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libyolo_b200.so')
+
+YB_F32, YB_BF16, YB_U8 = 0, 1, 2
+ACT_NONE, ACT_SILU, ACT_LEAKY = 0, 1, 2
+OP_CONV, OP_MAXPOOL2, OP_POOL_S1, OP_SPP3, OP_UPSAMPLE2, OP_COPY, OP_ADD = 1, 2, 3, 4, 5, 6, 7
+MAX_LEVELS, MAX_ANCHORS = 8, 8
+
+EXPORTS = [
+    'yb_last_error', 'yb_abi_version', 'yb_conv2d', 'yb_maxpool2x2', 'yb_maxpool_s1', 'yb_spp3',
+    'yb_upsample2x', 'yb_copy', 'yb_add', 'yb_stage_input', 'yb_decode', 'yb_nms_workspace_bytes',
+    'yb_nms', 'yb_decode_nms', 'yb_engine_create', 'yb_engine_forward', 'yb_engine_num_launches',
+    'yb_engine_destroy',
+]
+
+
+class Tensor(C.Structure):
+    _fields_ = [('data', C.c_void_p), ('dtype', C.c_int32), ('N', C.c_int32), ('H', C.c_int32),
+                ('W', C.c_int32), ('C', C.c_int32), ('c_stride', C.c_int32)]
+
+
+class ConvDesc(C.Structure):
+    _fields_ = [('x', Tensor), ('y', Tensor), ('weight', C.c_void_p), ('bias', C.c_void_p),
+                ('cin_pad', C.c_int32), ('cout_pad', C.c_int32), ('k', C.c_int32), ('stride', C.c_int32),
+                ('act', C.c_int32), ('leaky_slope', C.c_float), ('upsample', C.c_int32), ('res', Tensor),
+                ('tile_n', C.c_int32), ('stages', C.c_int32)]
+
+
+class HeadLevel(C.Structure):
+    _fields_ = [('logits', Tensor), ('stride', C.c_float), ('anchor_wh', C.c_float * (2 * MAX_ANCHORS))]
+
+
+class Op(C.Structure):
+    _fields_ = [('kind', C.c_int32), ('in0', C.c_int32), ('in1', C.c_int32), ('out0', C.c_int32),
+                ('out1', C.c_int32), ('out2', C.c_int32), ('k', C.c_int32), ('stride', C.c_int32),
+                ('act', C.c_int32), ('upsample', C.c_int32), ('leaky_slope', C.c_float), ('weight', C.c_int32),
+                ('cin_pad', C.c_int32), ('cout_pad', C.c_int32), ('tile_n', C.c_int32), ('stages', C.c_int32)]
+
+
+_lib = None
+
+
+def lib():
+    """Load (once) and return the ctypes handle.  Raises if the extension has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f'{LIB_PATH} is missing: build it with `python -c "import __graft_entry__ as g; '
+                           f'g.build()"` or `make -C yolo_series_b200/csrc`. There is no CPU fallback.')
+    L = C.CDLL(LIB_PATH)
+    L.yb_last_error.restype = C.c_char_p
+    L.yb_nms_workspace_bytes.restype = C.c_size_t
+    L.yb_nms_workspace_bytes.argtypes = [C.c_int] * 5
+    L.yb_engine_destroy.restype = None
+    L.yb_engine_destroy.argtypes = [C.c_void_p]
+    L.yb_engine_forward.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    L.yb_engine_num_launches.argtypes = [C.c_void_p]
+    L.yb_conv2d.argtypes = [C.POINTER(ConvDesc), C.c_void_p]
+    for name in ('yb_maxpool2x2', 'yb_upsample2x', 'yb_copy'):
+        getattr(L, name).argtypes = [C.POINTER(Tensor), C.POINTER(Tensor), C.c_void_p]
+    L.yb_maxpool_s1.argtypes = [C.POINTER(Tensor), C.POINTER(Tensor), C.c_int, C.c_void_p]
+    L.yb_spp3.argtypes = [C.POINTER(Tensor)] * 4 + [C.c_void_p]
+    L.yb_add.argtypes = [C.POINTER(Tensor)] * 3 + [C.c_void_p]
+    L.yb_stage_input.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                 C.POINTER(Tensor), C.c_void_p]
+    L.yb_decode.argtypes = [C.POINTER(HeadLevel), C.c_int, C.c_int, C.c_int, C.c_void_p,
+                            C.POINTER(C.c_void_p), C.c_void_p]
+    L.yb_nms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_double, C.POINTER(C.c_int), C.c_int,
+                         C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p,
+                         C.c_void_p, C.c_void_p, C.c_void_p]
+    L.yb_decode_nms.argtypes = [C.POINTER(HeadLevel), C.c_int, C.c_int, C.c_int, C.c_float, C.c_double,
+                                C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.yb_engine_create.argtypes = [C.POINTER(Tensor), C.c_int, C.POINTER(Op), C.c_int, C.POINTER(C.c_void_p),
+                                   C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_void_p)]
+    if L.yb_abi_version() != 1:
+        raise RuntimeError('libyolo_b200.so ABI version mismatch; rebuild')
+    _lib = L
+    return L
+
+
+def check(rc, what=''):
+    if rc != 0:
+        msg = lib().yb_last_error().decode('utf-8', 'replace')
+        raise RuntimeError(f'{what or "libyolo_b200"} failed (status {rc}): {msg}')
+
+
+def torch_dtype_code(t):
+    import torch
+    return {torch.float32: YB_F32, torch.bfloat16: YB_BF16, torch.uint8: YB_U8}[t]
+
+
+def view(t, c_off=0, C_=None):
+    """Describe a contiguous NHWC torch tensor (N,H,W,Cbuf) or a channel slice of it."""
+    n, h, w, cb = t.shape
+    c = cb - c_off if C_ is None else C_
+    return Tensor(t.data_ptr() + c_off * t.element_size(), torch_dtype_code(t.dtype), n, h, w, c, cb)
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,148 @@
+"""Shape-specialised instance of a lowered graph: HBM buffers, packed weights, C-side launch list.
+
+Memory layout (DESIGN.md "data layout in HBM"): every root tensor is its own contiguous NHWC
+buffer ``(B, H, W, C)`` in bf16 (trunk) or fp32 (fp32 reference mode; head logits are always fp32);
+concat members are channel slices of their consumer's buffer.  Nothing is re-used between layers:
+at yolov7/640/B=32 the whole activation set is 5.5 GB of the 180 GB HBM3e, so a liveness planner
+would only add risk.  Weights are packed ``[Cout][kh*kw][Cin_pad]`` in the trunk dtype, bias fp32.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import OP_CONV, YB_BF16, YB_F32, YB_U8
+
+
+def _round_up(x, m):
+    return (x + m - 1) // m * m
+
+
+class Engine:
+    def __init__(self, lowered, B, H, W, device, dtype=torch.bfloat16, use_graph=True, tile_overrides=None):
+        if device.type != 'cuda':
+            raise RuntimeError('yolo_series_b200 runs on CUDA (sm_100a) only; there is no CPU fallback')
+        self.L, self.B, self.H, self.W = lowered, B, H, W
+        self.device, self.dtype, self.use_graph = device, dtype, use_graph
+        self.lib = _lib.lib()
+        L = lowered
+        cpad_in = 16 if dtype == torch.bfloat16 else 4
+        # ---- buffers
+        self.buffers = {}
+        self.views = []
+
+        def root_of(v):
+            off = 0
+            while L.vals[v].parent is not None:
+                off += L.vals[v].offset
+                v = L.vals[v].parent
+            return v, off
+
+        used = set()
+        for op in L.ops:
+            used.update(op.ins)
+            used.update(op.outs)
+        used.add(L.input_val)
+        used.update(L.head_vals)
+        used.update(L.aux_vals)
+        for v in L.vals:
+            if v.vid not in used:
+                self.views.append(None)
+                continue
+            r, off = root_of(v.vid)
+            rv = L.vals[r]
+            if r not in self.buffers:
+                h, w = H * rv.num // rv.den, W * rv.num // rv.den
+                if r == L.input_val:
+                    cb = _round_up(rv.C, cpad_in)
+                else:
+                    cb = _round_up(rv.C, 8)
+                dt = torch.float32 if rv.f32 else dtype
+                self.buffers[r] = torch.zeros((B, h, w, cb), dtype=dt, device=device)
+            buf = self.buffers[r]
+            cview = buf.shape[3] if v.vid == L.input_val else v.C
+            self.views.append(_lib.view(buf, off, cview))
+        # ---- weights
+        self.weights, self.biases, self._keep = [], [], []
+        ops_c = (_lib.Op * len(L.ops))()
+        for i, op in enumerate(L.ops):
+            o = ops_c[i]
+            o.kind = op.kind
+            o.in0 = op.ins[0]
+            o.in1 = op.ins[1] if len(op.ins) > 1 else -1
+            o.out0 = op.outs[0]
+            o.out1 = op.outs[1] if len(op.outs) > 1 else -1
+            o.out2 = op.outs[2] if len(op.outs) > 2 else -1
+            o.k, o.stride, o.act, o.upsample, o.leaky_slope, o.weight = op.k, 1, 0, op.upsample, 0.0, -1
+            if op.kind == OP_CONV:
+                fc = op.conv
+                xin = self.views[op.ins[0]]
+                cin_pad = max(_round_up(fc.c_in, 8 if dtype == torch.bfloat16 else 4), xin.C)
+                if dtype == torch.bfloat16:
+                    cin_pad = max(cin_pad, 16)
+                w = torch.zeros((fc.c_out, fc.k * fc.k, cin_pad), dtype=torch.float32)
+                w[:, :, :fc.c_in] = fc.weight.permute(0, 2, 3, 1).reshape(fc.c_out, fc.k * fc.k, fc.c_in)
+                wd = w.to(device=device, dtype=dtype).contiguous()
+                bd = fc.bias.to(device=device, dtype=torch.float32).contiguous()
+                self.weights.append(wd)
+                self.biases.append(bd)
+                o.weight = len(self.weights) - 1
+                o.k, o.stride, o.act, o.leaky_slope = fc.k, fc.s, fc.act, fc.slope
+                o.cin_pad, o.cout_pad = cin_pad, fc.c_out
+                if tile_overrides and op.name in tile_overrides:
+                    o.tile_n, o.stages = tile_overrides[op.name]
+        tens_c = (_lib.Tensor * len(self.views))()
+        for i, v in enumerate(self.views):
+            if v is not None:
+                tens_c[i] = v
+        nw = len(self.weights)
+        w_ptrs = (C.c_void_p * max(nw, 1))(*[w.data_ptr() for w in self.weights])
+        b_ptrs = (C.c_void_p * max(nw, 1))(*[b.data_ptr() for b in self.biases])
+        handle = C.c_void_p()
+        _lib.check(self.lib.yb_engine_create(tens_c, len(self.views), ops_c, len(L.ops), w_ptrs, b_ptrs, nw,
+                                             C.byref(handle)), 'yb_engine_create')
+        self.handle = handle
+        self.n_ops = len(L.ops)
+        self.head = [self.buffers[v] for v in L.head_vals]        # fp32 NHWC logits per level
+        self.head_views = [self.views[v] for v in L.head_vals]
+        self.input_view = self.views[L.input_val]
+        self.conv_flops = self._count_flops()
+
+    def _count_flops(self):
+        total = 0
+        for op in self.L.ops:
+            if op.kind == OP_CONV:
+                fc = op.conv
+                v = self.L.vals[op.ins[0]]
+                ho = (self.H * v.num // v.den) // fc.s
+                wo = (self.W * v.num // v.den) // fc.s
+                total += 2 * fc.c_in * fc.c_out * fc.k * fc.k * ho * wo
+        return total  # per image
+
+    def stage(self, img):
+        """img: (B, C, H, W) uint8 or float32 CUDA tensor -> staged NHWC input buffer."""
+        if img.dtype not in (torch.uint8, torch.float32):
+            img = img.float()
+        img = img.contiguous()
+        code = YB_U8 if img.dtype == torch.uint8 else YB_F32
+        b, c, h, w = img.shape
+        if (b, h, w) != (self.B, self.H, self.W):
+            raise ValueError(f'engine built for {(self.B, self.H, self.W)}, got {(b, h, w)}')
+        _lib.check(self.lib.yb_stage_input(C.c_void_p(img.data_ptr()), code, b, c, h, w, int(self.L.reorg),
+                                           C.byref(self.input_view), _lib.stream_ptr()), 'yb_stage_input')
+
+    def run(self):
+        _lib.check(self.lib.yb_engine_forward(self.handle, int(self.use_graph), _lib.stream_ptr()),
+                   'yb_engine_forward')
+
+    def num_launches(self):
+        return self.lib.yb_engine_num_launches(self.handle)
+
+    def __del__(self):
+        h = getattr(self, 'handle', None)
+        if h:
+            try:
+                self.lib.yb_engine_destroy(h)
+            except Exception:
+                pass
+            self.handle = None

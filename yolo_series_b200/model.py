@@ -1,0 +1,313 @@
+"""Drop-in ``Model`` for the reference's ``models.yolo.Model`` (models/yolo.py:508-733), running the
+forward pass on the B200 engine.
+
+Same constructor ``Model(cfg, ch=3, nc=None, anchors=None)`` (yolo.py:509), same call
+``model(x, augment=False, profile=False)`` (yolo.py:581) returning the eval tuple
+``(pred (B, A, no), [raw_i (B, na, ny, nx, no)])`` (yolo.py:174), same attributes callers read
+(``stride``, ``names``, ``yaml``, ``model``, ``save``, ``model[-1].nl/na/nc/no/anchors/anchor_grid``,
+``fuse()``, ``half()/float()/to()/eval()``, ``parameters()``) -- see SURVEY.md 8(b).
+
+``accelerate(ref_model)`` wraps an already-built reference ``Model`` (e.g. unpickled by
+``attempt_load``, models/experimental.py:247-270) without re-creating it.
+"""
+import ctypes as C
+import math
+import os
+from copy import deepcopy
+
+import torch
+import torch.nn as nn
+
+from . import _lib, modules, plan, zoo
+from .engine import Engine
+
+
+def make_divisible(x, divisor):
+    return math.ceil(x / divisor) * divisor
+
+
+def _resolve_arg(a, scope):
+    """cfg strings are python expressions in the reference (yolo.py:744-749): support the ones the
+    yolov7 cfgs use without eval()."""
+    if not isinstance(a, str):
+        return a
+    if a in scope:
+        return scope[a]
+    if a == 'None':
+        return None
+    if a.startswith('nn.LeakyReLU'):
+        inner = a[a.index('(') + 1:a.rindex(')')].strip()
+        return nn.LeakyReLU(float(inner) if inner else 0.01)
+    if a in ('nn.SiLU()', 'nn.SiLU'):
+        return nn.SiLU()
+    if a in ('nn.Identity()',):
+        return nn.Identity()
+    return a  # e.g. 'nearest'
+
+
+def parse_model(d, ch):
+    """cfg dict -> (nn.Sequential of parameter containers with .i/.f/.type/.np, save list).
+    Grammar: SURVEY.md A.3 / reference yolo.py:736-813."""
+    anchors, nc, gd, gw = d['anchors'], d['nc'], d['depth_multiple'], d['width_multiple']
+    na = (len(anchors[0]) // 2) if isinstance(anchors, list) else anchors
+    no = na * (nc + 5)
+    scope = {'nc': nc, 'anchors': anchors}
+    layers, save, c2 = [], [], ch[-1]
+    for i, (f, n, mname, args) in enumerate(d['backbone'] + d['head']):
+        if mname not in modules.REGISTRY:
+            raise NotImplementedError(f'cfg node {i}: module {mname!r} is outside the yolov7 hot path')
+        cls = modules.REGISTRY[mname]
+        args = [_resolve_arg(a, scope) for a in args]
+        n = max(round(n * gd), 1) if n > 1 else n
+        if mname in modules.CONV_LIKE:
+            c1, c2 = ch[f], args[0]
+            if c2 != no:
+                c2 = make_divisible(c2 * gw, 8)
+            args = [c1, c2, *args[1:]]
+            if mname in ('DownC', 'SPPCSPC'):
+                args.insert(2, n)
+                n = 1
+        elif mname == 'Concat':
+            c2 = sum(ch[x] for x in f)
+        elif mname == 'Shortcut':
+            c2 = ch[f[0]]
+        elif mname in ('Detect', 'IDetect', 'IAuxDetect'):
+            args.append([ch[x] for x in f])
+            if isinstance(args[1], int):
+                args[1] = [list(range(args[1] * 2))] * len(f)
+        elif mname == 'ReOrg':
+            c2 = ch[f] * 4
+        else:
+            c2 = ch[f]
+        if n != 1:
+            raise NotImplementedError('depth repeats > 1 do not occur in the yolov7 cfgs')
+        m_ = cls(*args)
+        m_.i, m_.f, m_.type = i, f, mname
+        m_.np = sum(x.numel() for x in m_.parameters())
+        save.extend(x % i for x in ([f] if isinstance(f, int) else f) if x != -1)
+        layers.append(m_)
+        if i == 0:
+            ch = []
+        ch.append(c2)
+    return nn.Sequential(*layers), sorted(save)
+
+
+def _node_strides(layers):
+    """Spatial reduction of every node output vs the input (replaces the 256x256 dry run of
+    yolo.py:535-536)."""
+    red = []
+    for idx, m in enumerate(layers):
+        f = m.f
+        srcs = [idx + j if j < 0 else j for j in ([f] if isinstance(f, int) else f)]
+        r_in = 1.0 if idx == 0 else red[srcs[0]]
+        kind = type(m).__name__
+        if kind in ('Conv', 'RepConv'):
+            conv = m.conv if hasattr(m, 'conv') else (m.rbr_reparam if hasattr(m, 'rbr_reparam') else m.rbr_dense[0])
+            r = r_in * conv.stride[0]
+        elif kind in ('MP', 'DownC', 'ReOrg'):
+            r = r_in * 2
+        elif kind == 'Upsample':
+            r = r_in / 2
+        else:
+            r = r_in
+        red.append(r)
+    return red
+
+
+class Model(nn.Module):
+    def __init__(self, cfg='yolov7', ch=3, nc=None, anchors=None):
+        super().__init__()
+        self.traced = False
+        if isinstance(cfg, dict):
+            self.yaml = deepcopy(cfg)
+        elif isinstance(cfg, str) and os.path.exists(cfg):
+            import yaml
+            self.yaml_file = os.path.basename(cfg)
+            with open(cfg) as f:
+                self.yaml = yaml.safe_load(f)
+        else:
+            self.yaml = zoo.get_cfg(cfg)
+            self.yaml_file = str(cfg)
+        ch = self.yaml['ch'] = self.yaml.get('ch', ch)
+        if nc and nc != self.yaml['nc']:
+            self.yaml['nc'] = nc
+        if anchors:
+            self.yaml['anchors'] = round(anchors)
+        self.model, self.save = parse_model(deepcopy(self.yaml), ch=[ch])
+        self.names = [str(i) for i in range(self.yaml['nc'])]
+        head = self.model[-1]
+        if not isinstance(head, modules.HEADS):
+            raise NotImplementedError('last node must be Detect / IDetect / IAuxDetect')
+        red = _node_strides(self.model)
+        srcs = [len(self.model) - 1 + j if j < 0 else j for j in head.f]
+        head.stride = torch.tensor([float(red[s]) for s in srcs[:head.nl]])
+        self._check_anchor_order(head)
+        head.anchors /= head.stride.view(-1, 1, 1)
+        self.stride = head.stride
+        self._init_head_biases(head)
+        for m in self.modules():
+            if isinstance(m, nn.BatchNorm2d):     # utils/torch_utils.py:150-151
+                m.eps, m.momentum = 1e-3, 0.03
+        self._fused = False
+        self._engines = {}
+        self._compute_dtype = torch.bfloat16
+        self.use_graph = True
+
+    # ---- construction helpers (yolo.py:633-655, utils/autoanchor.py:12-20)
+    @staticmethod
+    def _check_anchor_order(m):
+        a = m.anchor_grid.prod(-1).view(-1)
+        if (a[-1] - a[0]).sign() != (m.stride[-1] - m.stride[0]).sign():
+            m.anchors[:] = m.anchors.flip(0)
+            m.anchor_grid[:] = m.anchor_grid.flip(0)
+
+    @staticmethod
+    def _init_head_biases(m):
+        convs = list(zip(m.m, m.stride)) + (list(zip(m.m2, m.stride)) if hasattr(m, 'm2') else [])
+        with torch.no_grad():
+            for mi, s in convs:
+                b = mi.bias.view(m.na, -1)
+                b[:, 4] += math.log(8 / (640 / float(s)) ** 2)
+                b[:, 5:] += math.log(0.6 / (m.nc - 0.99))
+
+    # ---- reference-compatible surface
+    def fuse(self):
+        """Folding happens when the engine is built; this only records the request (yolo.py:693-710)."""
+        self._invalidate()
+        return self
+
+    def half(self):
+        self._compute_dtype = torch.bfloat16   # fp16 on the reference (detect.py:49); bf16 here
+        self._invalidate()
+        return self
+
+    def float(self):
+        self._compute_dtype = torch.float32
+        self._invalidate()
+        return self
+
+    def set_precision(self, mode):
+        """'bf16' (tcgen05 tensor cores, default) or 'fp32' (CUDA-core reference mode)."""
+        self._compute_dtype = {'bf16': torch.bfloat16, 'fp32': torch.float32}[mode]
+        self._invalidate()
+        return self
+
+    def load_state_dict(self, *a, **k):
+        out = super().load_state_dict(*a, **k)
+        self._invalidate()
+        return out
+
+    def _invalidate(self):
+        self._engines = {}
+        self._lowered = None
+
+    def info(self, verbose=False, img_size=640):
+        n = sum(p.numel() for p in self.parameters())
+        print(f'Model Summary: {len(list(self.modules()))} layers, {n} parameters')
+
+    # ---- engine plumbing
+    def _layers(self):
+        return self.model
+
+    def _is_ref_fused(self):
+        return False
+
+    def _get_engine(self, B, H, W, device):
+        key = (B, H, W, str(device), self._compute_dtype)
+        eng = self._engines.get(key)
+        if eng is None:
+            if getattr(self, '_lowered', None) is None:
+                with torch.no_grad():
+                    self._lowered = plan.lower(self._layers(), in_ch=self.yaml.get('ch', 3),
+                                               fused=self._is_ref_fused())
+            eng = Engine(self._lowered, B, H, W, device, self._compute_dtype, self.use_graph,
+                         getattr(self, 'tile_overrides', None))
+            self._engines[key] = eng
+        return eng
+
+    def _device(self):
+        p = next(self.parameters())
+        return p.device
+
+    def head_levels(self, eng):
+        head = self._layers()[-1]
+        lv = (_lib.HeadLevel * head.nl)()
+        ag = head.anchor_grid.detach().float().cpu().view(head.nl, -1, 2)
+        for i in range(head.nl):
+            lv[i].logits = eng.head_views[i]
+            lv[i].stride = float(head.stride[i])
+            for a in range(head.na):
+                lv[i].anchor_wh[2 * a] = float(ag[i, a, 0])
+                lv[i].anchor_wh[2 * a + 1] = float(ag[i, a, 1])
+        return lv, head
+
+    def run_trunk(self, x):
+        """Stage + trunk + head convs.  Returns the engine (its ``head`` buffers hold the logits)."""
+        if x.device.type != 'cuda':
+            dev = self._device()
+            if dev.type != 'cuda':
+                raise RuntimeError('yolo_series_b200.Model needs a CUDA device: move the model or the input '
+                                   'to cuda (no CPU fallback)')
+            x = x.to(dev, non_blocking=True)
+        B, _, H, W = x.shape
+        gs = int(self.stride.max())
+        if H % gs or W % gs:
+            raise ValueError(f'input {H}x{W} must be a multiple of the max stride {gs} (general.py:124-129)')
+        eng = self._get_engine(B, H, W, x.device)
+        eng.stage(x)
+        eng.run()
+        return eng
+
+    @torch.no_grad()
+    def forward(self, x, augment=False, profile=False):
+        if augment:
+            raise NotImplementedError('TTA (yolo.py:582-597) is a "next" row (SURVEY.md 8f), not built yet')
+        eng = self.run_trunk(x)
+        lv, head = self.head_levels(eng)
+        A = sum(head.na * v.H * v.W for v in eng.head_views)
+        pred = torch.empty((eng.B, A, head.no), dtype=torch.float32, device=eng.device)
+        raws = [torch.empty((eng.B, head.na, v.H, v.W, head.no), dtype=torch.float32, device=eng.device)
+                for v in eng.head_views]
+        raw_ptrs = (C.c_void_p * head.nl)(*[r.data_ptr() for r in raws])
+        _lib.check(eng.lib.yb_decode(lv, head.nl, head.na, head.no, C.c_void_p(pred.data_ptr()), raw_ptrs,
+                                     _lib.stream_ptr()), 'yb_decode')
+        return pred, raws
+
+    @torch.no_grad()
+    def detect(self, x, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False, multi_label=False,
+               max_det=300, max_nms=30000):
+        """Fused fast path: forward + decode + NMS without materialising ``pred`` (yb_decode_nms).
+        Returns the same list as ``non_max_suppression(model(x)[0], ...)``."""
+        from .nms import _run_nms
+        eng = self.run_trunk(x)
+        lv, head = self.head_levels(eng)
+        A = sum(head.na * v.H * v.W for v in eng.head_views)
+        return _run_nms(None, eng.B, A, head.no, conf_thres, iou_thres, classes, agnostic, multi_label, max_nms,
+                        max_det, eng.device, levels=(lv, head.nl, head.na))
+
+
+class AcceleratedModel(Model):
+    """Wraps an existing reference ``Model`` instance (duck-typed) -- see ``accelerate``."""
+
+    def __init__(self, ref_model):
+        nn.Module.__init__(self)
+        self.ref = ref_model
+        self.traced = False
+        self.yaml = getattr(ref_model, 'yaml', {'ch': 3})
+        self.model = ref_model.model
+        self.save = getattr(ref_model, 'save', [])
+        self.names = getattr(ref_model, 'names', None)
+        self.stride = ref_model.stride
+        self._engines, self._lowered = {}, None
+        self._compute_dtype = torch.bfloat16
+        self.use_graph = True
+
+    def _is_ref_fused(self):
+        head = self.model[-1]
+        # the reference's fuse() swaps forward for fuseforward (yolo.py:705,708)
+        return getattr(getattr(head, 'forward', None), '__name__', '') == 'fuseforward'
+
+
+def accelerate(ref_model):
+    """Return a drop-in module whose forward runs on the B200 engine using ``ref_model``'s weights."""
+    return AcceleratedModel(ref_model)
