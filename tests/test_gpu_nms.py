@@ -107,9 +107,10 @@ def test_decode_matches_torch_and_fused_path():
     for a, b in zip(raw_gpu, raws):
         assert torch.equal(a.cpu(), b)
     p = pred.cpu()
-    ulp = torch.abs(p - ref) / torch.clamp(torch.abs(ref), min=1e-30)
-    assert float(ulp.max()) < 4 * 1.2e-7 * 8, float(ulp.max())   # xy: (2p-0.5+g) cancellation amplifies sigmoid ulps
-    assert torch.allclose(p, ref, rtol=2e-6, atol=1e-5)
+    # obj/cls are the bare sigmoid: <= 2 ulp of fp32 (values in (0,1): 1 ulp <= 6e-8)
+    assert float((p[..., 4:] - ref[..., 4:]).abs().max()) <= 2 * 6e-8
+    # xy/wh: the same 2-ulp sigmoid error scaled by 2*stride / 4*anchor*(2p): <= 2e-4 px here
+    assert torch.allclose(p[..., :4], ref[..., :4], rtol=1e-6, atol=2e-4)
     # fused path: identical rows to NMS over the GPU-decoded pred
     from yolo_series_b200 import non_max_suppression
     a = non_max_suppression(pred, 0.05, 0.5, max_det=300)

@@ -43,12 +43,17 @@ def act_code(act):
     raise NotImplementedError(f'activation {type(act).__name__} is not on the yolov7 hot path')
 
 
+def _f(t):
+    """fp32 CPU copy (folding is host-side, whatever device the module lives on)."""
+    return t.detach().float().cpu()
+
+
 def _bn_scale_shift(bn):
-    std = torch.sqrt(bn.running_var.float() + bn.eps)
-    gamma = bn.weight.float() if bn.weight is not None else torch.ones_like(std)
-    beta = bn.bias.float() if bn.bias is not None else torch.zeros_like(std)
+    std = torch.sqrt(_f(bn.running_var) + bn.eps)
+    gamma = _f(bn.weight) if bn.weight is not None else torch.ones_like(std)
+    beta = _f(bn.bias) if bn.bias is not None else torch.zeros_like(std)
     scale = gamma / std
-    return scale, beta - bn.running_mean.float() * scale
+    return scale, beta - _f(bn.running_mean) * scale
 
 
 def _conv_geometry(conv):
@@ -63,8 +68,8 @@ def _conv_geometry(conv):
 @torch.no_grad()
 def fold_conv_bn(conv, bn):
     """(W', b') of conv followed by eval-mode BatchNorm; bn may be None (already fused module)."""
-    w = conv.weight.float()
-    b = conv.bias.float() if conv.bias is not None else torch.zeros(w.shape[0])
+    w = _f(conv.weight)
+    b = _f(conv.bias) if conv.bias is not None else torch.zeros(w.shape[0])
     if bn is None:
         return w.clone(), b.clone()
     scale, shift = _bn_scale_shift(bn)
@@ -89,7 +94,7 @@ def fold_repconv(m):
     a, sl = act_code(m.act)
     if hasattr(m, 'rbr_reparam'):
         k, s = _conv_geometry(m.rbr_reparam)
-        return FoldedConv(m.rbr_reparam.weight.float().clone(), m.rbr_reparam.bias.float().clone(), k, s, a, sl)
+        return FoldedConv(_f(m.rbr_reparam.weight).clone(), _f(m.rbr_reparam.bias).clone(), k, s, a, sl)
     dense_conv, dense_bn = m.rbr_dense[0], m.rbr_dense[1]
     one_conv, one_bn = m.rbr_1x1[0], m.rbr_1x1[1]
     s = dense_conv.stride[0]
@@ -122,11 +127,11 @@ def fold_head(head, fused):
     out = []
     for i in range(head.nl):
         conv = head.m[i]
-        w = conv.weight.float().clone()
-        b = conv.bias.float().clone()
+        w = _f(conv.weight).clone()
+        b = _f(conv.bias).clone()
         if not fused and hasattr(head, 'ia'):
-            ia = head.ia[i].implicit.float().view(-1)
-            im = head.im[i].implicit.float().view(-1)
+            ia = _f(head.ia[i].implicit).view(-1)
+            im = _f(head.im[i].implicit).view(-1)
             b = b + w.view(w.shape[0], -1) @ ia
             b = b * im
             w = w * im.view(-1, 1, 1, 1)
