@@ -171,6 +171,8 @@ int yb_engine_create(const yb_tensor* tensors, int n_tensors, const yb_op* ops, 
                      yb_engine** out);
 /* launch every op on `stream`; use_graph != 0 replays a CUDA graph captured on first use */
 int yb_engine_forward(yb_engine* e, int use_graph, void* stream);
+/* eager run with a CUDA event between consecutive ops; ms_per_op[n_ops] (synchronises `stream`) */
+int yb_engine_profile(yb_engine* e, float* ms_per_op, void* stream);
 int yb_engine_num_launches(const yb_engine* e);
 void yb_engine_destroy(yb_engine* e);
 

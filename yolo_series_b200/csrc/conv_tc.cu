@@ -36,6 +36,7 @@ struct ConvTcArgs {
   int sw_mode;                     // UMMA layout type: 2 = SW128, 4 = SW64, 6 = SW32
   int tmem_cols;
   int bias_len;
+  int total_tiles;
   uint32_t idesc;
 };
 
@@ -116,12 +117,33 @@ __device__ __forceinline__ float act_fast(float v, int act, float slope) {
   return v;
 }
 
-constexpr int kTcThreads = 192;
+constexpr int kEpiWarps = 8;                       // two warps per TMEM lane quarter, each takes half the columns
+constexpr int kTcThreads = 64 + 32 * kEpiWarps;    // warp 0 producer, warp 1 MMA, warps 2.. epilogue
+constexpr int kMaxBias = 2048;
 
-__global__ void __launch_bounds__(kTcThreads) k_conv_tc(const __grid_constant__ ConvTcArgs G) {
+// SiLU with ONE MUFU op per element: x*sigmoid(x) = 0.5x*tanh(0.5x) + 0.5x (tanh.approx rel. err ~2^-11 << bf16 ulp)
+__device__ __forceinline__ float silu_fast(float v) {
+  const float h = 0.5f * v;
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+  return fmaf(h, t, h);
+}
+__device__ __forceinline__ float act_epi(float v, int act, float slope) {
+  if (act == YB_ACT_SILU) return silu_fast(v);
+  if (act == YB_ACT_LEAKY) return v > 0.f ? v : v * slope;
+  return v;
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+// Persistent kernel: one CTA per SM walks tiles t = blockIdx.x, +gridDim.x, ...  The TMA producer runs
+// ahead across tile boundaries (smem ring of `stages` K-chunks), accumulators are double-buffered in
+// TMEM so the MMA of tile i+1 overlaps the epilogue of tile i, and the epilogue owns a dedicated
+// swizzled staging buffer for the TMA store.
+__global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant__ ConvTcArgs G) {
   extern __shared__ unsigned char smem_dyn[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // ---- carve shared memory: [tiles (1024-aligned)] [barriers] [tmem ptr] [bias]
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
   unsigned char* tiles_ptr = smem_dyn + (tiles - raw);
@@ -129,32 +151,22 @@ __global__ void __launch_bounds__(kTcThreads) k_conv_tc(const __grid_constant__ 
   const uint32_t b_bytes = (uint32_t)G.BN * G.BK * 2u;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t out_es = G.out_f32 ? 4u : 2u;
-  uint32_t pipe_bytes = stage_bytes * G.stages;
-  const uint32_t stage_out_bytes = 128u * G.BN * out_es;
-  if (pipe_bytes < stage_out_bytes) pipe_bytes = stage_out_bytes;
-  unsigned char* aux = tiles_ptr + pipe_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(aux);            // full[stages], empty[stages], tmem_full
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux + 8 * (2 * G.stages + 1));
-  float* bias_s = reinterpret_cast<float*>(aux + 8 * (2 * G.stages + 1) + 16);
+  const uint32_t pipe_bytes = stage_bytes * G.stages;
+  const uint32_t staging = tiles + pipe_bytes;                       // 1024-aligned (stage_bytes % 1024 == 0)
+  const uint32_t staging_bytes = 128u * G.BN * out_es;
+  unsigned char* aux = tiles_ptr + pipe_bytes + staging_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(aux);  // full[S], empty[S], tmem_full[2], tmem_empty[2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux + 8 * (2 * G.stages + 4));
+  float* bias_s = reinterpret_cast<float*>(aux + 8 * (2 * G.stages + 4) + 16);
   const uint32_t bar_full0 = smem_u32(bars), bar_empty0 = bar_full0 + 8u * G.stages;
-  const uint32_t bar_tmem = bar_full0 + 16u * G.stages;
-
-  // ---- tile coordinates
-  const int n_tile = blockIdx.x % G.tiles_n;
-  int m_tile = blockIdx.x / G.tiles_n;
-  const int tw = m_tile % G.tiles_w;
-  m_tile /= G.tiles_w;
-  const int th = m_tile % G.tiles_h;
-  const int img = m_tile / G.tiles_h;
-  const int n0 = n_tile * G.BN;
-  const int w0 = tw * G.BW, h0 = th * G.BH;
+  const uint32_t bar_tfull0 = bar_full0 + 16u * G.stages, bar_tempty0 = bar_tfull0 + 16u;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&G.tm_a);
     tma_prefetch_desc(&G.tm_b);
     for (int i = 0; i < G.n_store_maps; ++i) tma_prefetch_desc(&G.tm_y[i]);
     for (int s = 0; s < G.stages; ++s) { mbar_init(bar_full0 + 8u * s, 1); mbar_init(bar_empty0 + 8u * s, 1); }
-    mbar_init(bar_tmem, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull0 + 8u * i, 1); mbar_init(bar_tempty0 + 8u * i, 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -162,109 +174,140 @@ __global__ void __launch_bounds__(kTcThreads) k_conv_tc(const __grid_constant__ 
                  "r"((uint32_t)G.tmem_cols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  if (warp >= 2) {
-    for (int i = threadIdx.x - 64; i < G.BN; i += 128) bias_s[i] = (n0 + i < G.bias_len) ? G.bias[n0 + i] : 0.f;
-  }
+  for (int i = threadIdx.x; i < kMaxBias; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
   const int total_chunks = G.taps * G.kchunks;
+  const int tiles_m_per_img = G.tiles_w * G.tiles_h;
 
   if (warp == 0) {
     // ================================ TMA producer ================================
     if (lane == 0) {
       const uint32_t tx = (uint32_t)(G.BW * G.BH) * G.BK * 2u + b_bytes;
-      int kc = 0;
-      for (int tap = 0; tap < G.taps; ++tap) {
-        const int dy = tap / G.ksz, dx = tap - dy * G.ksz;
-        const int cw = w0 * G.stride + dx - G.pad;
-        const int chh = G.flat ? 0 : h0 * G.stride + dy - G.pad;
-        for (int kk = 0; kk < G.kchunks; ++kk, ++kc) {
-          const int s = kc % G.stages;
-          const uint32_t ph = (uint32_t)(kc / G.stages) & 1u;
-          mbar_wait(bar_empty0 + 8u * s, ph ^ 1u);
-          const uint32_t full = bar_full0 + 8u * s;
-          mbar_expect_tx(full, tx);
-          const uint32_t sa = tiles + s * stage_bytes;
-          tma_load_4d(&G.tm_a, full, sa, kk * G.BK, cw, chh, img);
-          tma_load_3d(&G.tm_b, full, sa + a_bytes, kk * G.BK, tap, n0);
+      uint32_t kc = 0;  // running chunk counter across tiles -> ring slot + phase
+      for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x) {
+        const int n_tile = t % G.tiles_n;
+        int m_tile = t / G.tiles_n;
+        const int img = m_tile / tiles_m_per_img;
+        m_tile -= img * tiles_m_per_img;
+        const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+        const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
+        for (int tap = 0; tap < G.taps; ++tap) {
+          const int dy = tap / G.ksz, dx = tap - dy * G.ksz;
+          const int cw = w0 * G.stride + dx - G.pad;
+          const int chh = G.flat ? 0 : h0 * G.stride + dy - G.pad;
+          for (int kk = 0; kk < G.kchunks; ++kk, ++kc) {
+            const uint32_t s = kc % (uint32_t)G.stages;
+            const uint32_t ph = (kc / (uint32_t)G.stages) & 1u;
+            mbar_wait(bar_empty0 + 8u * s, ph ^ 1u);
+            const uint32_t full = bar_full0 + 8u * s;
+            mbar_expect_tx(full, tx);
+            const uint32_t sa = tiles + s * stage_bytes;
+            tma_load_4d(&G.tm_a, full, sa, kk * G.BK, cw, chh, img);
+            tma_load_3d(&G.tm_b, full, sa + a_bytes, kk * G.BK, tap, n0);
+          }
         }
       }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
     if (lane == 0) {
-      const uint32_t row_bytes = (uint32_t)G.BK * 2u;
-      const uint32_t sbo = 8u * row_bytes;
-      for (int kc = 0; kc < total_chunks; ++kc) {
-        const int s = kc % G.stages;
-        const uint32_t ph = (uint32_t)(kc / G.stages) & 1u;
-        mbar_wait(bar_full0 + 8u * s, ph);
+      const uint32_t sbo = 8u * (uint32_t)G.BK * 2u;
+      const int nk = G.BK / 16;
+      uint32_t kc = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
+        const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
+        mbar_wait(bar_tempty0 + 8u * acc, aph ^ 1u);       // epilogue has drained this accumulator
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t sa = tiles + s * stage_bytes;
-        const uint64_t da = make_smem_desc(sa, sbo, (uint32_t)G.sw_mode);
-        const uint64_t db = make_smem_desc(sa + a_bytes, sbo, (uint32_t)G.sw_mode);
-        const int nk = G.BK / 16;
-        for (int k = 0; k < nk; ++k) {
-          // advance 16 K-elements = 32 bytes inside the swizzle span: +2 in the (addr >> 4) field
-          umma_bf16(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), G.idesc, (uint32_t)((kc | k) != 0));
+        const uint32_t tmem_d = tmem_base + acc * (uint32_t)G.BN;
+        for (int c = 0; c < total_chunks; ++c, ++kc) {
+          const uint32_t s = kc % (uint32_t)G.stages;
+          const uint32_t ph = (kc / (uint32_t)G.stages) & 1u;
+          mbar_wait(bar_full0 + 8u * s, ph);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t sa = tiles + s * stage_bytes;
+          const uint64_t da = make_smem_desc(sa, sbo, (uint32_t)G.sw_mode);
+          const uint64_t db = make_smem_desc(sa + a_bytes, sbo, (uint32_t)G.sw_mode);
+          for (int k = 0; k < nk; ++k)
+            umma_bf16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), G.idesc, (uint32_t)((c | k) != 0));
+          umma_commit(bar_empty0 + 8u * s);
         }
-        umma_commit(bar_empty0 + 8u * s);  // frees the smem stage once these MMAs retire
+        umma_commit(bar_tfull0 + 8u * acc);
       }
-      umma_commit(bar_tmem);               // accumulator complete
     }
   } else {
     // ================================ epilogue ====================================
+    const int ew = warp - 2;
     const int q = warp & 3;                 // TMEM lane quarter this warp may read
-    const int row = q * 32 + lane;          // pixel row inside the tile
-    mbar_wait(bar_tmem, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int half = ew >> 2;               // which half of the 32-column chunks this warp owns
+    const int row = q * 32 + lane;
     const uint32_t xr = (uint32_t)(row & 7);
     const int nchunks = G.BN / 32;
-    for (int cc = 0; cc < nchunks; ++cc) {
-      uint32_t v[32];
-      tmem_ld32(taddr + (uint32_t)(cc * 32), v);
-      float f[32];
+    const int c_begin = (kEpiWarps == 8) ? (half * ((nchunks + 1) / 2)) : 0;
+    const int c_end = (kEpiWarps == 8) ? (half == 0 ? (nchunks + 1) / 2 : nchunks) : nchunks;
+    const bool store_thread = (warp == 2 && lane == 0);
+    int it = 0;
+    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
+      const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
+      const int n_tile = t % G.tiles_n;
+      int m_tile = t / G.tiles_n;
+      const int img = m_tile / tiles_m_per_img;
+      m_tile -= img * tiles_m_per_img;
+      const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+      const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
+      mbar_wait(bar_tfull0 + 8u * acc, aph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging free again
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)G.BN;
+      for (int cc = c_begin; cc < c_end; ++cc) {
+        uint32_t v[32];
+        tmem_ld32(taddr + (uint32_t)(cc * 32), v);
+        float f[32];
+        const float* bs = bias_s + n0 + cc * 32;
 #pragma unroll
-      for (int i = 0; i < 32; ++i) f[i] = act_fast(__uint_as_float(v[i]) + bias_s[cc * 32 + i], G.act, G.slope);
-      if (G.out_f32) {
-        const uint32_t base = tiles + (uint32_t)cc * 16384u + (uint32_t)row * 128u;
+        for (int i = 0; i < 32; ++i) f[i] = act_epi(__uint_as_float(v[i]) + bs[i], G.act, G.slope);
+        if (G.out_f32) {
+          const uint32_t base = staging + (uint32_t)cc * 16384u + (uint32_t)row * 128u;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t addr = base + ((((uint32_t)j) ^ xr) << 4);
-          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(f[4 * j]), "f"(f[4 * j + 1]),
-                       "f"(f[4 * j + 2]), "f"(f[4 * j + 3]) : "memory");
-        }
-      } else {
-        const uint32_t base = tiles + (uint32_t)(cc >> 1) * 16384u + (uint32_t)row * 128u;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint32_t p[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            __nv_bfloat162 h = __floats2bfloat162_rn(f[8 * j + 2 * e], f[8 * j + 2 * e + 1]);
-            p[e] = *reinterpret_cast<uint32_t*>(&h);
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t addr = base + ((((uint32_t)j) ^ xr) << 4);
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(f[4 * j]), "f"(f[4 * j + 1]),
+                         "f"(f[4 * j + 2]), "f"(f[4 * j + 3]) : "memory");
           }
-          const uint32_t addr = base + ((((uint32_t)((cc & 1) * 4 + j)) ^ xr) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(p[0]), "r"(p[1]), "r"(p[2]),
-                       "r"(p[3]) : "memory");
+        } else {
+          const uint32_t base = staging + (uint32_t)(cc >> 1) * 16384u + (uint32_t)row * 128u;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t p[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              __nv_bfloat162 hh = __floats2bfloat162_rn(f[8 * j + 2 * e], f[8 * j + 2 * e + 1]);
+              p[e] = *reinterpret_cast<uint32_t*>(&hh);
+            }
+            const uint32_t addr = base + ((((uint32_t)((cc & 1) * 4 + j)) ^ xr) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(p[0]), "r"(p[1]), "r"(p[2]),
+                         "r"(p[3]) : "memory");
+          }
         }
       }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to TMA
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+      if (store_thread) {
+        mbar_arrive(bar_tempty0 + 8u * acc);   // every epilogue warp has finished reading this accumulator
+        const int per_group = G.out_f32 ? 32 : 64;
+        const int ngroups = (G.BN + per_group - 1) / per_group;
+        for (int mp = 0; mp < G.n_store_maps; ++mp)
+          for (int g = 0; g < ngroups; ++g)
+            tma_store_4d(&G.tm_y[mp], staging + (uint32_t)g * 16384u, n0 + g * per_group, w0, G.flat ? 0 : h0, img);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
     }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to TMA
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    if (warp == 2 && lane == 0) {
-      const int per_group = G.out_f32 ? 32 : 64;
-      const int ngroups = (G.BN + per_group - 1) / per_group;
-      for (int mp = 0; mp < G.n_store_maps; ++mp)
-        for (int g = 0; g < ngroups; ++g)
-          tma_store_4d(&G.tm_y[mp], tiles + (uint32_t)g * 16384u, n0 + g * per_group, w0, G.flat ? 0 : h0, img);
-      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-    }
+    if (store_thread) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   __syncthreads();
   if (warp == 1) {
@@ -320,14 +363,25 @@ struct ConvTcPlan {
   size_t smem;
 };
 
-static int pick_tile_n(int cout) {
+// Tile-N heuristic: estimated cycles = rounds of the persistent grid x per-tile cost, where a tile costs
+// max(MMA issue, operand bytes / ~42 B/clk/SM of L2->smem TMA throughput, epilogue) -- see DESIGN.md.
+static int pick_tile_n(int cout, long long m_tiles, int chunks, int bk, bool out_f32) {
   if (cout <= 32) return 32;
-  int best = 64, best_cost = 1 << 30;
   const int cands[3] = {64, 128, 256};
-  for (int i = 0; i < 2; ++i) {  // 256 only by explicit override for now
-    int bn = cands[i];
-    int cost = (cout + bn - 1) / bn * bn;
-    if (cost < best_cost || (cost == best_cost && bn > best)) { best = bn; best_cost = cost; }
+  int best = 64;
+  double best_cost = 1e30;
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cands[i];
+    if (out_f32 && bn > 128) continue;  // fp32 staging tile would not leave room for the pipeline
+    const long long tiles = m_tiles * ((cout + bn - 1) / bn);
+    const double rounds = (double)((tiles + num_sms() - 1) / num_sms());
+    const double mma = chunks * (bk / 16) * (bn / 2.0);
+    const double load = chunks * (128.0 * bk * 2 + (double)bn * bk * 2) / 42.0;
+    const double epi = bn * 10.0 + 600.0;
+    double tile = mma > load ? mma : load;
+    if (epi > tile) tile = epi;
+    const double cost = rounds * (tile + 400.0);
+    if (cost < best_cost * 0.999) { best_cost = cost; best = bn; }
   }
   return best;
 }
@@ -360,9 +414,6 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   A.sw_mode = A.BK == 64 ? 2 : (A.BK == 32 ? 4 : 6);
   const CUtensorMapSwizzle sw_in = A.BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
                                               : (A.BK == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
-  A.BN = d.tile_n ? d.tile_n : pick_tile_n(Cout);
-  YB_CHECK_ARG(A.BN == 32 || A.BN == 64 || A.BN == 128 || A.BN == 256, "conv(tc): tile_n must be 32/64/128/256");
-  A.tiles_n = (Cout + A.BN - 1) / A.BN;
   A.flat = (k == 1 && s == 1 && ups == 1) ? 1 : 0;
   int images = x.N;
   if (A.flat) {
@@ -384,20 +435,24 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
     A.tiles_w = (Wo + A.BW - 1) / A.BW;
     A.tiles_h = (Ho + A.BH - 1) / A.BH;
   }
+  A.BN = d.tile_n ? d.tile_n : pick_tile_n(Cout, (long long)A.tiles_w * A.tiles_h * images, A.taps * A.kchunks, A.BK,
+                                          y.dtype == YB_F32);
+  YB_CHECK_ARG(A.BN == 32 || A.BN == 64 || A.BN == 128 || A.BN == 256, "conv(tc): tile_n must be 32/64/128/256");
+  A.tiles_n = (Cout + A.BN - 1) / A.BN;
   A.n_store_maps = ups == 2 ? 4 : 1;
-  A.tmem_cols = A.BN < 32 ? 32 : A.BN;
+  A.tmem_cols = 2 * A.BN < 32 ? 32 : 2 * A.BN;   // double-buffered accumulators (64/128/256/512 columns)
   A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
   // stages / shared memory
   const size_t stage_bytes = (size_t)128 * A.BK * 2 + (size_t)A.BN * A.BK * 2;
-  const size_t budget = A.BN >= 256 ? 200 * 1024 : 100 * 1024;
+  const size_t stage_out = (size_t)128 * A.BN * y_es;
+  const size_t aux_bytes = 8 * (2 * 12 + 4) + 16 + (size_t)kMaxBias * 4 + 64;
+  const size_t budget = 226 * 1024 - 1024 - stage_out - aux_bytes;
   int stages = d.stages ? d.stages : (int)(budget / stage_bytes);
-  if (stages > 8) stages = 8;
-  if (stages > A.taps * A.kchunks) stages = A.taps * A.kchunks;
-  if (stages < 1) stages = 1;
+  if (stages > 12) stages = 12;
+  if (stages < 2) stages = 2;
   A.stages = stages;
-  size_t pipe = stage_bytes * stages, stage_out = (size_t)128 * A.BN * y_es;
-  if (pipe < stage_out) pipe = stage_out;
-  P->smem = 1024 + pipe + 8 * (2 * stages + 1) + 16 + (size_t)A.BN * 4 + 64;
+  P->smem = 1024 + stage_bytes * stages + stage_out + aux_bytes;
+  YB_CHECK_ARG(d.cout_pad <= kMaxBias, "conv(tc): cout_pad > %d unsupported", kMaxBias);
   if (P->smem > 227 * 1024) {
     set_error("conv(tc): shared memory budget exceeded (%zu bytes)", P->smem);
     delete P;
@@ -462,7 +517,8 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   YB_CHECK_ARG(y.H == Ho * ups && y.W == Wo * ups && y.N == x.N, "conv(tc): output spatial dims mismatch");
   const long long grid = (long long)A.tiles_n * A.tiles_w * A.tiles_h * images;
   YB_CHECK_ARG(grid < 0x7fffffffLL, "conv(tc): grid too large");
-  P->grid = (int)grid;
+  A.total_tiles = (int)grid;
+  P->grid = (int)(grid < num_sms() ? grid : num_sms());
   *out = P;
   return YB_OK;
 }

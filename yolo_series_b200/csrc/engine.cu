@@ -20,9 +20,10 @@ struct yb_engine {
 
 namespace yb {
 
-static int run_ops(yb_engine* e, cudaStream_t s) {
+static int run_ops(yb_engine* e, cudaStream_t s, cudaEvent_t* evs = nullptr) {
   int launches = 0;
   for (size_t i = 0; i < e->ops.size(); ++i) {
+    if (evs) cudaEventRecord(evs[i], s);
     const yb_op& o = e->ops[i];
     auto T = [&](int idx) -> const yb_tensor* { return idx >= 0 ? &e->tensors[idx] : nullptr; };
     int rc = YB_OK;
@@ -52,6 +53,7 @@ static int run_ops(yb_engine* e, cudaStream_t s) {
     if (rc) return rc;
     ++launches;
   }
+  if (evs) cudaEventRecord(evs[e->ops.size()], s);
   e->launches = launches;
   return YB_OK;
 }
@@ -122,6 +124,22 @@ extern "C" int yb_engine_forward(yb_engine* e, int use_graph, void* stream) {
   }
   YB_CUDA(cudaGraphLaunch(e->graph_exec, s));
   return YB_OK;
+}
+
+extern "C" int yb_engine_profile(yb_engine* e, float* ms_per_op, void* stream) {
+  YB_CHECK_ARG(e && ms_per_op, "yb_engine_profile: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t n = e->ops.size();
+  std::vector<cudaEvent_t> evs(n + 1);
+  for (auto& ev : evs) YB_CUDA(cudaEventCreate(&ev));
+  int rc = run_ops(e, s, evs.data());
+  if (!rc) {
+    cudaError_t ce = cudaStreamSynchronize(s);
+    if (ce != cudaSuccess) { set_error("yb_engine_profile: %s", cudaGetErrorString(ce)); rc = YB_ERR_CUDA; }
+  }
+  for (size_t i = 0; i < n && !rc; ++i) cudaEventElapsedTime(&ms_per_op[i], evs[i], evs[i + 1]);
+  for (auto& ev : evs) cudaEventDestroy(ev);
+  return rc;
 }
 
 extern "C" int yb_engine_num_launches(const yb_engine* e) { return e ? e->launches : 0; }

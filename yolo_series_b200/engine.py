@@ -135,6 +135,22 @@ class Engine:
         _lib.check(self.lib.yb_engine_forward(self.handle, int(self.use_graph), _lib.stream_ptr()),
                    'yb_engine_forward')
 
+    def profile(self):
+        """Per-op device time (ms) of one eager pass, with op descriptions: [(name, kind, ms, flops)]."""
+        ms = (C.c_float * self.n_ops)()
+        _lib.check(self.lib.yb_engine_profile(self.handle, ms, _lib.stream_ptr()), 'yb_engine_profile')
+        rows = []
+        for i, op in enumerate(self.L.ops):
+            fl = 0
+            if op.kind == OP_CONV:
+                fc = op.conv
+                v = self.L.vals[op.ins[0]]
+                ho = (self.H * v.num // v.den) // fc.s
+                wo = (self.W * v.num // v.den) // fc.s
+                fl = 2 * fc.c_in * fc.c_out * fc.k * fc.k * ho * wo * self.B
+            rows.append((op.name, op.kind, float(ms[i]), fl))
+        return rows
+
     def num_launches(self):
         return self.lib.yb_engine_num_launches(self.handle)
 

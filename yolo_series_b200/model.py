@@ -275,15 +275,16 @@ class Model(nn.Module):
 
     @torch.no_grad()
     def detect(self, x, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False, multi_label=False,
-               max_det=300, max_nms=30000):
+               max_det=300, max_nms=30000, packed=False):
         """Fused fast path: forward + decode + NMS without materialising ``pred`` (yb_decode_nms).
-        Returns the same list as ``non_max_suppression(model(x)[0], ...)``."""
+        Returns the same list as ``non_max_suppression(model(x)[0], ...)``; ``packed=True`` returns the device
+        buffers ``(out (B,max_det,6), meta int32 [counts..., overflow])`` with no host synchronisation."""
         from .nms import _run_nms
         eng = self.run_trunk(x)
         lv, head = self.head_levels(eng)
         A = sum(head.na * v.H * v.W for v in eng.head_views)
         return _run_nms(None, eng.B, A, head.no, conf_thres, iou_thres, classes, agnostic, multi_label, max_nms,
-                        max_det, eng.device, levels=(lv, head.nl, head.na))
+                        max_det, eng.device, levels=(lv, head.nl, head.na), return_packed=packed)
 
 
 class AcceleratedModel(Model):
