@@ -202,7 +202,6 @@ def main():
     model = model.to(dev).eval().half()          # bf16 trunk (reference: model.half(), detect.py:49)
     x_host = synth_image(B, IMG, IMG, seed=100 + rank, dtype=torch.uint8).pin_memory()
     x_dev = x_host.to(dev)
-    x_dev2 = torch.empty_like(x_dev)
 
     def step_device():
         out, meta = model.detect(x_dev, CONF, IOU, max_det=MAX_DET, packed=True)
@@ -211,8 +210,8 @@ def main():
         return out, meta
 
     def step_e2e():
-        x_dev2.copy_(x_host, non_blocking=True)                  # H2D from pinned memory, every step
-        out, meta = model.detect(x_dev2, CONF, IOU, max_det=MAX_DET, packed=True)
+        # the pinned host batch is copied H2D straight into the engine's input buffer, every step
+        out, meta = model.detect(x_host, CONF, IOU, max_det=MAX_DET, packed=True)
         cnt = meta[:B]
         if world > 1:
             out, cnt = ydist.gather_detections(out, cnt)

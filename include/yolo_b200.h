@@ -102,6 +102,13 @@ int yb_add(const yb_tensor* a, const yb_tensor* b, const yb_tensor* y, void* str
 int yb_stage_input(const void* img, int img_dtype, int B, int C, int H, int W, int reorg,
                    const yb_tensor* y, void* stream);
 
+/* Fused staging + first conv for the bf16 path: reads the NCHW uint8/fp32 image directly (optionally
+ * through ReOrg), 3x3 conv (stride 1|2) + bias + activation, writes NHWC bf16.  Same result as
+ * yb_stage_input followed by yb_conv2d on bf16 operands (weights [Cout][9][cin_pad] bf16). */
+int yb_stem_conv(const void* img, int img_dtype, int B, int C, int H, int W, int reorg,
+                 const void* weight, const float* bias, int cin_pad, int stride, int act,
+                 float leaky_slope, const yb_tensor* y, void* stream);
+
 /* ------------------------------------------------------------------ head decode
  * IDetect.fuseforward inference branch (models/yolo.py:145-162; arithmetic SURVEY.md A.5).
  * Each level: logits NHWC (B, ny, nx, >= na*no), channel index a*no + o.
@@ -150,7 +157,8 @@ int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no, float con
  */
 typedef enum {
   YB_OP_CONV = 1, YB_OP_MAXPOOL2 = 2, YB_OP_POOL_S1 = 3, YB_OP_SPP3 = 4, YB_OP_UPSAMPLE2 = 5,
-  YB_OP_COPY = 6, YB_OP_ADD = 7
+  YB_OP_COPY = 6, YB_OP_ADD = 7,
+  YB_OP_STEM = 8 /* in0 = raw NCHW image tensor (dtype u8|f32, c_stride ignored); tile_n carries the ReOrg flag */
 } yb_op_kind;
 
 typedef struct {

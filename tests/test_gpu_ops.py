@@ -117,3 +117,26 @@ def test_stage_input_and_reorg():
     a = ref
     want = torch.cat([a[..., ::2, ::2], a[..., 1::2, ::2], a[..., ::2, 1::2], a[..., 1::2, 1::2]], 1)
     assert torch.equal(_nchw(r.cpu())[:, :12], want) and torch.all(r[..., 12:] == 0)
+
+
+@pytest.mark.parametrize('cfg', [(3, 32, 1, False, 48, 160), (3, 32, 2, False, 64, 200), (3, 64, 1, True, 64, 96),
+                                 (3, 80, 1, True, 32, 288)], ids=['v7', 'tiny_s2', 'w6_reorg', 'e6e_reorg'])
+@pytest.mark.parametrize('u8', [True, False])
+def test_stem_conv_fused_staging(cfg, u8):
+    """Fused staging + first conv (mma.sync path) vs fp32 conv of the bf16-rounded operands."""
+    from yolo_series_b200 import ops
+    C_, Co, s, reorg, H, W = cfg
+    g = torch.Generator().manual_seed(6)
+    img = torch.randint(0, 256, (2, C_, H, W), generator=g, dtype=torch.uint8)
+    x = img.float() / 255.0
+    src = img if u8 else x
+    if reorg:
+        x = torch.cat([x[..., ::2, ::2], x[..., 1::2, ::2], x[..., ::2, 1::2], x[..., 1::2, 1::2]], 1)
+    ci = x.shape[1]
+    w = (torch.randn((Co, ci, 3, 3), generator=g) / (ci * 9) ** 0.5).bfloat16().float()
+    b = torch.randn((Co,), generator=g)
+    ref = F.silu(F.conv2d(x.bfloat16().float(), w, b, s, 1))
+    y = ops.stem_conv(src.cuda(), w, b, s, 1, 0.0, reorg)
+    got = _nchw(y.float().cpu())
+    assert got.shape == ref.shape
+    assert torch.allclose(got, ref, rtol=1.2e-2, atol=1.2e-2), float((got - ref).abs().max())

@@ -12,12 +12,12 @@ LIB_PATH = os.path.join(_HERE, 'libyolo_b200.so')
 
 YB_F32, YB_BF16, YB_U8 = 0, 1, 2
 ACT_NONE, ACT_SILU, ACT_LEAKY = 0, 1, 2
-OP_CONV, OP_MAXPOOL2, OP_POOL_S1, OP_SPP3, OP_UPSAMPLE2, OP_COPY, OP_ADD = 1, 2, 3, 4, 5, 6, 7
+OP_CONV, OP_MAXPOOL2, OP_POOL_S1, OP_SPP3, OP_UPSAMPLE2, OP_COPY, OP_ADD, OP_STEM = 1, 2, 3, 4, 5, 6, 7, 8
 MAX_LEVELS, MAX_ANCHORS = 8, 8
 
 EXPORTS = [
     'yb_last_error', 'yb_abi_version', 'yb_conv2d', 'yb_maxpool2x2', 'yb_maxpool_s1', 'yb_spp3',
-    'yb_upsample2x', 'yb_copy', 'yb_add', 'yb_stage_input', 'yb_decode', 'yb_nms_workspace_bytes',
+    'yb_upsample2x', 'yb_copy', 'yb_add', 'yb_stage_input', 'yb_stem_conv', 'yb_decode', 'yb_nms_workspace_bytes',
     'yb_nms', 'yb_decode_nms', 'yb_engine_create', 'yb_engine_forward', 'yb_engine_num_launches', 'yb_engine_profile',
     'yb_engine_destroy',
 ]
@@ -74,6 +74,8 @@ def lib():
     L.yb_add.argtypes = [C.POINTER(Tensor)] * 3 + [C.c_void_p]
     L.yb_stage_input.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                  C.POINTER(Tensor), C.c_void_p]
+    L.yb_stem_conv.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                               C.c_int, C.c_int, C.c_int, C.c_float, C.POINTER(Tensor), C.c_void_p]
     L.yb_decode.argtypes = [C.POINTER(HeadLevel), C.c_int, C.c_int, C.c_int, C.c_void_p,
                             C.POINTER(C.c_void_p), C.c_void_p]
     L.yb_nms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_double, C.POINTER(C.c_int), C.c_int,

@@ -48,6 +48,12 @@ static int run_ops(yb_engine* e, cudaStream_t s, cudaEvent_t* evs = nullptr) {
       case YB_OP_UPSAMPLE2: rc = yb_upsample2x(T(o.in0), T(o.out0), s); break;
       case YB_OP_COPY: rc = yb_copy(T(o.in0), T(o.out0), s); break;
       case YB_OP_ADD: rc = yb_add(T(o.in0), T(o.in1), T(o.out0), s); break;
+      case YB_OP_STEM: {
+        const yb_tensor* im = T(o.in0);
+        rc = yb_stem_conv(im->data, im->dtype, im->N, im->C, im->H, im->W, o.tile_n, e->weights[o.weight],
+                          e->biases[o.weight], o.cin_pad, o.stride, o.act, o.leaky_slope, T(o.out0), s);
+        break;
+      }
       default: set_error("engine: unknown op kind %d at %zu", o.kind, i); return YB_ERR_INVALID;
     }
     if (rc) return rc;
@@ -82,13 +88,13 @@ extern "C" int yb_engine_create(const yb_tensor* tensors, int n_tensors, const y
       yb_engine_destroy(e);
       return YB_ERR_INVALID;
     }
-    if (o.kind != YB_OP_CONV) continue;
+    if (o.kind != YB_OP_CONV && o.kind != YB_OP_STEM) continue;
     if (o.weight < 0 || o.weight >= n_weights) {
       set_error("yb_engine_create: op %d has an invalid weight index", i);
       yb_engine_destroy(e);
       return YB_ERR_INVALID;
     }
-    if (e->tensors[o.in0].dtype != YB_BF16) continue;
+    if (o.kind == YB_OP_STEM || e->tensors[o.in0].dtype != YB_BF16) continue;
     yb_conv_desc d;
     memset(&d, 0, sizeof(d));
     d.x = e->tensors[o.in0]; d.y = e->tensors[o.out0];

@@ -11,7 +11,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import OP_CONV, YB_BF16, YB_F32, YB_U8
+from ._lib import OP_CONV, OP_STEM, YB_BF16, YB_F32, YB_U8
 
 
 def _round_up(x, m):
@@ -19,7 +19,8 @@ def _round_up(x, m):
 
 
 class Engine:
-    def __init__(self, lowered, B, H, W, device, dtype=torch.bfloat16, use_graph=True, tile_overrides=None):
+    def __init__(self, lowered, B, H, W, device, dtype=torch.bfloat16, use_graph=True, tile_overrides=None,
+                 img_dtype=torch.uint8, fuse_stem=True):
         if device.type != 'cuda':
             raise RuntimeError('yolo_series_b200 runs on CUDA (sm_100a) only; there is no CPU fallback')
         self.L, self.B, self.H, self.W = lowered, B, H, W
@@ -62,6 +63,18 @@ class Engine:
             buf = self.buffers[r]
             cview = buf.shape[3] if v.vid == L.input_val else v.C
             self.views.append(_lib.view(buf, off, cview))
+        # ---- fused staging + first conv (bf16 path): the stem kernel reads the raw NCHW image itself
+        self.img_buf, stem_op = None, None
+        if dtype == torch.bfloat16 and fuse_stem:
+            readers = [op for op in L.ops if L.input_val in op.ins]
+            if (len(readers) == 1 and readers[0].kind == OP_CONV and readers[0].conv.k == 3 and readers[0].upsample == 1
+                    and readers[0].conv.c_in <= 16 and readers[0].conv.c_out % 16 == 0 and readers[0].conv.c_out <= 96
+                    and not L.vals[readers[0].outs[0]].f32):
+                stem_op = readers[0]
+                self.img_buf = torch.zeros((B, L.in_ch, H, W), dtype=img_dtype, device=device)
+                self.views.append(_lib.Tensor(self.img_buf.data_ptr(), _lib.torch_dtype_code(img_dtype), B, H, W,
+                                              L.in_ch, L.in_ch))
+        self.img_dtype = img_dtype
         # ---- weights
         self.weights, self.biases, self._keep = [], [], []
         ops_c = (_lib.Op * len(L.ops))()
@@ -91,6 +104,8 @@ class Engine:
                 o.cin_pad, o.cout_pad = cin_pad, fc.c_out
                 if tile_overrides and op.name in tile_overrides:
                     o.tile_n, o.stages = tile_overrides[op.name]
+                if op is stem_op:
+                    o.kind, o.in0, o.tile_n = OP_STEM, len(self.views) - 1, int(L.reorg)
         tens_c = (_lib.Tensor * len(self.views))()
         for i, v in enumerate(self.views):
             if v is not None:
@@ -123,6 +138,14 @@ class Engine:
         """img: (B, C, H, W) uint8 or float32 CUDA tensor -> staged NHWC input buffer."""
         if img.dtype not in (torch.uint8, torch.float32):
             img = img.float()
+        if self.img_buf is not None:
+            if img.dtype != self.img_dtype or tuple(img.shape) != tuple(self.img_buf.shape):
+                raise ValueError(f'engine built for {tuple(self.img_buf.shape)} {self.img_dtype}, got '
+                                 f'{tuple(img.shape)} {img.dtype}')
+            self.img_buf.copy_(img, non_blocking=True)     # D2D, or H2D straight from (pinned) host memory
+            return
+        if img.device != self.device:
+            img = img.to(self.device, non_blocking=True)
         img = img.contiguous()
         code = YB_U8 if img.dtype == torch.uint8 else YB_F32
         b, c, h, w = img.shape

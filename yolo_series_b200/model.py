@@ -212,8 +212,8 @@ class Model(nn.Module):
     def _is_ref_fused(self):
         return False
 
-    def _get_engine(self, B, H, W, device):
-        key = (B, H, W, str(device), self._compute_dtype)
+    def _get_engine(self, B, H, W, device, img_dtype=torch.uint8):
+        key = (B, H, W, str(device), self._compute_dtype, img_dtype)
         eng = self._engines.get(key)
         if eng is None:
             if getattr(self, '_lowered', None) is None:
@@ -221,7 +221,8 @@ class Model(nn.Module):
                     self._lowered = plan.lower(self._layers(), in_ch=self.yaml.get('ch', 3),
                                                fused=self._is_ref_fused())
             eng = Engine(self._lowered, B, H, W, device, self._compute_dtype, self.use_graph,
-                         getattr(self, 'tile_overrides', None))
+                         getattr(self, 'tile_overrides', None), img_dtype=img_dtype,
+                         fuse_stem=getattr(self, 'fuse_stem', True))
             self._engines[key] = eng
         return eng
 
@@ -243,17 +244,19 @@ class Model(nn.Module):
 
     def run_trunk(self, x):
         """Stage + trunk + head convs.  Returns the engine (its ``head`` buffers hold the logits)."""
-        if x.device.type != 'cuda':
+        dev = x.device
+        if dev.type != 'cuda':
             dev = self._device()
             if dev.type != 'cuda':
                 raise RuntimeError('yolo_series_b200.Model needs a CUDA device: move the model or the input '
                                    'to cuda (no CPU fallback)')
-            x = x.to(dev, non_blocking=True)
+        if x.dtype not in (torch.uint8, torch.float32):
+            x = x.float()
         B, _, H, W = x.shape
         gs = int(self.stride.max())
         if H % gs or W % gs:
             raise ValueError(f'input {H}x{W} must be a multiple of the max stride {gs} (general.py:124-129)')
-        eng = self._get_engine(B, H, W, x.device)
+        eng = self._get_engine(B, H, W, dev, x.dtype)
         eng.stage(x)
         eng.run()
         return eng

@@ -121,3 +121,21 @@ def decode(logits, strides, anchor_grid, na, no, want_raw=True):
     ptrs = (C.c_void_p * nl)(*[r.data_ptr() for r in raws]) if want_raw else None
     _lib.check(L.yb_decode(lv, nl, na, no, C.c_void_p(pred.data_ptr()), ptrs, _lib.stream_ptr()), 'yb_decode')
     return pred, raws, (lv, nl, na)
+
+
+def stem_conv(img, w, b, stride=1, act=ACT_NONE, slope=0.0, reorg=False):
+    """img: (B,C,H,W) uint8|fp32 cuda; w: (Cout, Cin', 3, 3) fp32 with Cin' = C (or 4C with reorg)."""
+    L = _lib.lib()
+    B, C_, H, W = img.shape
+    co, ci = w.shape[0], w.shape[1]
+    hi, wi = (H // 2, W // 2) if reorg else (H, W)
+    ho, wo = (hi - 1) // stride + 1, (wi - 1) // stride + 1
+    wp = pack_weight(w.to(img.device), 16, torch.bfloat16)
+    bp = b.to(img.device, torch.float32).contiguous()
+    out = torch.zeros((B, ho, wo, co), dtype=torch.bfloat16, device=img.device)
+    vy = _lib.view(out)
+    code = _lib.YB_U8 if img.dtype == torch.uint8 else _lib.YB_F32
+    _lib.check(L.yb_stem_conv(C.c_void_p(img.data_ptr()), code, B, C_, H, W, int(reorg), C.c_void_p(wp.data_ptr()),
+                              C.c_void_p(bp.data_ptr()), 16, stride, act, slope, C.byref(vy), _lib.stream_ptr()),
+               'yb_stem_conv')
+    return out
