@@ -37,6 +37,10 @@ CONV_CASES = [
     (1, 20, 20, 512, 255, 1, 1, 0, 1),      # head conv (Cout 255)
     (1, 160, 160, 64, 64, 3, 1, 1, 1),      # wide map, many tiles
     (3, 12, 20, 96, 96, 3, 1, 1, 1),        # ragged tiles
+    (1, 40, 40, 32, 32, 3, 1, 2, 1),        # slab kernel, Cin 32 (SW64), LeakyReLU
+    (2, 40, 40, 128, 128, 3, 1, 1, 1),      # slab kernel, 40-wide map (120-pixel sub-tiles)
+    (1, 80, 80, 64, 192, 3, 1, 1, 1),       # slab kernel, 16x8 sub-tiles, 3 N tiles of 64
+    (2, 24, 24, 512, 64, 3, 1, 1, 1),       # slab kernel, 8 K chunks
 ]
 
 
@@ -140,3 +144,17 @@ def test_stem_conv_fused_staging(cfg, u8):
     got = _nchw(y.float().cpu())
     assert got.shape == ref.shape
     assert torch.allclose(got, ref, rtol=1.2e-2, atol=1.2e-2), float((got - ref).abs().max())
+
+
+@pytest.mark.parametrize('case', [(2, 20, 20, 128, 256, 3, 1, 1, 1), (1, 80, 80, 64, 192, 3, 1, 1, 1)], ids=str)
+def test_conv_tc_generic_kernel_on_3x3(case):
+    """tile_n = -1 forces the generic per-tap kernel for shapes the slab kernel normally takes."""
+    from yolo_series_b200 import ops
+    N, H, W, Ci, Co, k, s, act, ups = case
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn((N, Ci, H, W), generator=g).bfloat16().float()
+    w = (torch.randn((Co, Ci, k, k), generator=g) / (Ci * k * k) ** 0.5).bfloat16().float()
+    b = torch.randn((Co,), generator=g)
+    ref = _ref_conv(x, w, b, s, act, 0.1, ups)
+    y = ops.conv2d(_nhwc(x).cuda().bfloat16(), w, b, s, act, 0.1, ups, tile_n=-1)
+    assert torch.allclose(_nchw(y[..., :Co].float().cpu()), ref, rtol=1.2e-2, atol=1.2e-2)

@@ -77,4 +77,9 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out);
 int conv_tc_launch(const ConvTcPlan* p, cudaStream_t s);
 void conv_tc_plan_destroy(ConvTcPlan* p);
 
+struct Conv3Plan;   // 3x3 stride-1 slab kernel (conv3_tc.cu); plan_create returns YB_ERR_UNSUPPORTED to decline
+int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out);
+int conv3_tc_launch(const Conv3Plan* p, cudaStream_t s);
+void conv3_tc_plan_destroy(Conv3Plan* p);
+
 }  // namespace yb

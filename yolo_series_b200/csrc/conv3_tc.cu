@@ -1,0 +1,340 @@
+// 3x3 stride-1 convolution on tcgen05 with operand reuse in shared memory ("slab" kernel).
+//
+// The generic kernel (conv_tc.cu) loads one 128-pixel activation tile per filter tap: 9 loads of the
+// same pixels, and on B200 the 3x3 layers of yolov7 are bound by L2->smem TMA throughput, not by the
+// tensor pipe (profiles/round1_*).  This kernel cuts the operand bytes per MAC ~2.2x:
+//   * a CTA owns a SUPER-tile of 2 stacked 128-pixel sub-tiles (BW x 2*BH output pixels, BW % 8 == 0);
+//   * per K chunk and per filter COLUMN dx it loads ONE activation slab: box {BK ch, BW, 2*BH+2 rows}
+//     at (w0+dx-1, h0-1) -- hardware zero-fill gives the padding.  Because BW is a multiple of the
+//     8-row swizzle atom, the operand of filter row dy for sub-tile j is the same slab advanced by
+//     (j*BH + dy)*BW rows: only the UMMA descriptor start address changes, no data moves;
+//   * the three weight tiles (dy = 0..2) of that column are loaded once and feed both sub-tiles.
+// Bytes per (dx, chunk) stage: A (2BH+2)*BW*128 B (36 KB at 16x8) + B 3*BN*128 B, for 2*3*BK/16 MMAs.
+// TMEM: 2 sub-accumulators x 2 (double buffering) x BN columns (BN <= 128).
+// Same epilogue as conv_tc.cu (bias + SiLU/LeakyReLU -> bf16 -> swizzled staging -> TMA store into the
+// concat slice).  Reference op: Conv.fuseforward / fused RepConv, models/common.py:110-111, 498-500.
+#include "tc_common.cuh"
+
+namespace yb {
+
+struct Conv3Args {
+  CUtensorMap tm_a;
+  CUtensorMap tm_b;
+  CUtensorMap tm_y;
+  const float* bias;
+  int tiles_n, tiles_w, tiles_h;   // super-tile grid per image
+  int BW, BH, BN, BK;
+  int kchunks, stages;
+  int act; float slope;
+  int sw_mode, tmem_cols, bias_len, total_tiles;
+  uint32_t a_bytes;                // slab bytes, rounded up to 1024
+  uint32_t a_tx;                   // bytes the slab TMA actually delivers
+  uint32_t idesc;
+};
+
+// 18 * NK MMAs of one pipeline stage: 2 sub-tiles x 3 filter rows x NK 16-wide K steps.
+template <int NK>
+__device__ __forceinline__ void issue_stage(uint32_t tmem_d0, uint32_t bn, uint32_t dlo, uint32_t hi32,
+                                            const uint32_t (&aoff)[2][3], const uint32_t (&boff)[3],
+                                            uint32_t idesc, uint32_t acc0) {
+#pragma unroll
+  for (int j = 0; j < 2; ++j) {
+#pragma unroll
+    for (int dy = 0; dy < 3; ++dy) {
+#pragma unroll
+      for (int k = 0; k < NK; ++k)
+        umma_bf16_lh(tmem_d0 + (uint32_t)j * bn, dlo + aoff[j][dy] + (uint32_t)(2 * k),
+                     dlo + boff[dy] + (uint32_t)(2 * k), hi32, idesc, (dy | k) ? 1u : acc0);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constant__ Conv3Args G) {
+  extern __shared__ unsigned char smem_dyn[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t raw = smem_u32(smem_dyn);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;
+  unsigned char* tiles_ptr = smem_dyn + (tiles - raw);
+  const uint32_t row_bytes = (uint32_t)G.BK * 2u;
+  const uint32_t b_bytes = (uint32_t)G.BN * row_bytes;
+  const uint32_t stage_bytes = G.a_bytes + 3u * b_bytes;
+  const uint32_t pipe_bytes = stage_bytes * G.stages;
+  const uint32_t staging = tiles + pipe_bytes;
+  const uint32_t staging_bytes = (uint32_t)((G.BN + 63) / 64) * 16384u;   // 128 rows x 128 B per 64-channel group
+  unsigned char* aux = tiles_ptr + pipe_bytes + staging_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(aux);  // full[S], empty[S], tmem_full[2], tmem_empty[2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux + 8 * (2 * G.stages + 4));
+  float* bias_s = reinterpret_cast<float*>(aux + 8 * (2 * G.stages + 4) + 16);
+  const uint32_t bar_full0 = smem_u32(bars), bar_empty0 = bar_full0 + 8u * G.stages;
+  const uint32_t bar_tfull0 = bar_full0 + 16u * G.stages, bar_tempty0 = bar_tfull0 + 16u;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&G.tm_a);
+    tma_prefetch_desc(&G.tm_b);
+    tma_prefetch_desc(&G.tm_y);
+    for (int s = 0; s < G.stages; ++s) { mbar_init(bar_full0 + 8u * s, 1); mbar_init(bar_empty0 + 8u * s, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull0 + 8u * i, 1); mbar_init(bar_tempty0 + 8u * i, 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"((uint32_t)G.tmem_cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  for (int i = threadIdx.x; i < kMaxBias; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+  const int tiles_m_per_img = G.tiles_w * G.tiles_h;
+  const int stages_per_tile = 3 * G.kchunks;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    // Warp-uniform control flow, one elected lane issues the copies (coordinates live in uniform registers).
+    const uint32_t tx = G.a_tx + 3u * b_bytes;
+    uint32_t s = 0, ph = 1;  // ring slot + parity to wait for on its empty barrier
+    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x) {
+      const int n_tile = t % G.tiles_n;
+      int m_tile = t / G.tiles_n;
+      const int img = m_tile / tiles_m_per_img;
+      m_tile -= img * tiles_m_per_img;
+      const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+      const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * 2 * G.BH;
+      for (int kk = 0; kk < G.kchunks; ++kk) {
+#pragma unroll
+        for (int dx = 0; dx < 3; ++dx) {
+          mbar_wait(bar_empty0 + 8u * s, ph);
+          if (elect_one()) {
+            const uint32_t full = bar_full0 + 8u * s;
+            mbar_expect_tx(full, tx);
+            const uint32_t sa = tiles + s * stage_bytes;
+            tma_load_4d(&G.tm_a, full, sa, kk * G.BK, w0 + dx - 1, h0 - 1, img);
+#pragma unroll
+            for (int dy = 0; dy < 3; ++dy)
+              tma_load_3d(&G.tm_b, full, sa + G.a_bytes + (uint32_t)dy * b_bytes, kk * G.BK, dy * 3 + dx, n0);
+          }
+          __syncwarp();
+          if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ==================================
+    // Whole warp runs the (uniform) control flow; one elected lane issues tcgen05.mma / commit.
+    const uint32_t sbo = 8u * row_bytes;
+    const int nk = G.BK / 16;
+    const uint32_t sub_rows = (uint32_t)(G.BH * G.BW);   // rows between the two sub-tiles
+    const uint32_t hi32 = (uint32_t)(make_smem_desc(0, sbo, (uint32_t)G.sw_mode) >> 32);
+    uint32_t aoff[2][3], boff[3];                        // descriptor address-field offsets (bytes >> 4)
+#pragma unroll
+    for (int dy = 0; dy < 3; ++dy) {
+      boff[dy] = (G.a_bytes + (uint32_t)dy * b_bytes) >> 4;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) aoff[j][dy] = (((uint32_t)j * sub_rows + (uint32_t)(dy * G.BW)) * row_bytes) >> 4;
+    }
+    uint32_t s = 0, ph = 0;
+    int it = 0;
+    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
+      const uint32_t par = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
+      mbar_wait(bar_tempty0 + 8u * par, aph ^ 1u);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t tmem_d0 = tmem_base + (par * 2u) * (uint32_t)G.BN;
+      for (int c = 0; c < stages_per_tile; ++c) {
+        mbar_wait(bar_full0 + 8u * s, ph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t dlo = ((tiles + s * stage_bytes) >> 4) & 0x3FFF;
+        if (elect_one()) {
+          if (nk == 4) issue_stage<4>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, (uint32_t)(c != 0));
+          else         issue_stage<2>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, (uint32_t)(c != 0));
+          umma_commit(bar_empty0 + 8u * s);
+        }
+        __syncwarp();
+        if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
+      }
+      if (elect_one()) umma_commit(bar_tfull0 + 8u * par);
+      __syncwarp();
+    }
+  } else {
+    // ================================ epilogue ====================================
+    const int ew = warp - 2;
+    const int q = warp & 3;
+    const int half = ew >> 2;
+    const int row = q * 32 + lane;
+    const uint32_t xr = (uint32_t)(row & 7);
+    const int nchunks = G.BN / 32;
+    const int c_begin = half * ((nchunks + 1) / 2);
+    const int c_end = half == 0 ? (nchunks + 1) / 2 : nchunks;
+    const bool store_thread = (warp == 2 && lane == 0);
+    int it = 0;
+    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
+      const uint32_t par = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
+      const int n_tile = t % G.tiles_n;
+      int m_tile = t / G.tiles_n;
+      const int img = m_tile / tiles_m_per_img;
+      m_tile -= img * tiles_m_per_img;
+      const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+      const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * 2 * G.BH;
+      mbar_wait(bar_tfull0 + 8u * par, aph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      for (int j = 0; j < 2; ++j) {
+        if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging free again
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (par * 2u + (uint32_t)j) * (uint32_t)G.BN;
+        for (int cc = c_begin; cc < c_end; ++cc) {
+          uint32_t v[32];
+          tmem_ld32(taddr + (uint32_t)(cc * 32), v);
+          const float* bs = bias_s + n0 + cc * 32;
+          const uint32_t base = staging + (uint32_t)(cc >> 1) * 16384u + (uint32_t)row * 128u;
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) {
+            uint32_t p[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int i0 = 8 * jj + 2 * e;
+              const float f0 = act_epi(__uint_as_float(v[i0]) + bs[i0], G.act, G.slope);
+              const float f1 = act_epi(__uint_as_float(v[i0 + 1]) + bs[i0 + 1], G.act, G.slope);
+              __nv_bfloat162 hh = __floats2bfloat162_rn(f0, f1);
+              p[e] = *reinterpret_cast<uint32_t*>(&hh);
+            }
+            const uint32_t addr = base + ((((uint32_t)((cc & 1) * 4 + jj)) ^ xr) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(p[0]), "r"(p[1]), "r"(p[2]),
+                         "r"(p[3]) : "memory");
+          }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+        if (store_thread) {
+          if (j == 1) mbar_arrive(bar_tempty0 + 8u * par);   // both sub-accumulators have been read
+          const int ngroups = (G.BN + 63) / 64;
+          for (int g = 0; g < ngroups; ++g)
+            tma_store_4d(&G.tm_y, staging + (uint32_t)g * 16384u, n0 + g * 64, w0, h0 + j * G.BH, img);
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
+    }
+    if (store_thread) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G.tmem_cols)
+                 : "memory");
+  }
+}
+
+struct Conv3Plan {
+  Conv3Args args;
+  int grid;
+  size_t smem;
+};
+
+// Returns YB_ERR_UNSUPPORTED (without touching the error string semantics of real failures) when the shape
+// is better served by the generic kernel; the caller then falls back to conv_tc.
+int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
+  const yb_tensor& x = d.x;
+  const yb_tensor& y = d.y;
+  if (d.k != 3 || d.stride != 1 || d.upsample != 1 || x.dtype != YB_BF16 || y.dtype != YB_BF16 || d.res.data)
+    return YB_ERR_UNSUPPORTED;
+  const int Cin = x.C, Cout = y.C, H = x.H, W = x.W;
+  if (Cin < 32 || d.cin_pad < 32) return YB_ERR_UNSUPPORTED;
+  YB_CHECK_ARG(x.c_stride % 8 == 0 && d.cin_pad % 8 == 0 && (uintptr_t)x.data % 16 == 0 && (uintptr_t)d.weight % 16 == 0 &&
+                   y.c_stride % 8 == 0 && (uintptr_t)y.data % 16 == 0, "conv3(tc): alignment");
+  YB_CHECK_ARG(d.cout_pad <= kMaxBias, "conv3(tc): cout_pad > %d unsupported", kMaxBias);
+  Conv3Plan* P = new Conv3Plan();
+  Conv3Args& A = P->args;
+  memset(&A, 0, sizeof(A));
+  A.bias = d.bias; A.bias_len = d.cout_pad; A.act = d.act; A.slope = d.leaky_slope;
+  A.BK = Cin >= 64 ? 64 : 32;
+  A.kchunks = (Cin + A.BK - 1) / A.BK;
+  A.sw_mode = A.BK == 64 ? 2 : 4;
+  const CUtensorMapSwizzle sw_in = A.BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  // ---- spatial tile: BW multiple of 8, BH = 128 / BW (sub-tile <= 128 px), super-tile BW x 2BH
+  long long best_cost = -1;
+  const int bw_step = A.BK == 64 ? 8 : 16;   // sub-tile / filter-row offsets stay 1024-byte aligned
+  for (int bw = bw_step; bw <= 128; bw += bw_step) {
+    int bh = 128 / bw;
+    if (bh < 1) continue;
+    if (2 * bh + 2 > 256) continue;
+    const long long nt = (long long)((W + bw - 1) / bw) * ((H + 2 * bh - 1) / (2 * bh));
+    const long long cost = nt * ((2 * bh + 2) * bw + 96);   // slab rows (+ weight rows equivalent) per super-tile
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; A.BW = bw; A.BH = bh; }
+  }
+  A.tiles_w = (W + A.BW - 1) / A.BW;
+  A.tiles_h = (H + 2 * A.BH - 1) / (2 * A.BH);
+  if (d.tile_n) A.BN = d.tile_n;
+  else if (Cout <= 32) A.BN = 32;
+  else if (Cout <= 64) A.BN = 64;
+  else {
+    // 64 vs 128: fewer padded columns wins, ties -> 128 (halves the activation traffic)
+    const int c64 = (Cout + 63) / 64 * 64, c128 = (Cout + 127) / 128 * 128;
+    A.BN = c64 < c128 ? 64 : 128;
+  }
+  YB_CHECK_ARG(A.BN == 32 || A.BN == 64 || A.BN == 128, "conv3(tc): tile_n must be 32/64/128");
+  A.tiles_n = (Cout + A.BN - 1) / A.BN;
+  A.tmem_cols = 4 * A.BN < 32 ? 32 : 4 * A.BN;
+  A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  const uint32_t row_bytes = A.BK * 2;
+  A.a_tx = (uint32_t)(2 * A.BH + 2) * A.BW * row_bytes;
+  // the last sub-tile's MMA reads 128 rows from row (BH+2)*BW: keep those reads inside the stage
+  uint32_t need_rows = (uint32_t)((A.BH + 2) * A.BW + 128);
+  uint32_t slab_rows = (uint32_t)(2 * A.BH + 2) * A.BW;
+  if (need_rows > slab_rows) slab_rows = need_rows;
+  A.a_bytes = (uint32_t)align_up((size_t)slab_rows * row_bytes, 1024);
+  const size_t stage_bytes = (size_t)A.a_bytes + 3 * (size_t)A.BN * row_bytes;
+  const size_t stage_out = (size_t)((A.BN + 63) / 64) * 16384;
+  const size_t aux_bytes = 8 * (2 * 12 + 4) + 16 + (size_t)kMaxBias * 4 + 64;
+  const size_t budget = 226 * 1024 - 1024 - stage_out - aux_bytes;
+  int stages = d.stages ? d.stages : (int)(budget / stage_bytes);
+  if (stages > 12) stages = 12;
+  if (stages < 2) { delete P; return YB_ERR_UNSUPPORTED; }
+  A.stages = stages;
+  P->smem = 1024 + stage_bytes * stages + stage_out + aux_bytes;
+  const uint32_t one4[4] = {1, 1, 1, 1};
+  int rc;
+  {
+    const uint64_t cs = (uint64_t)x.c_stride * 2;
+    uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)x.N};
+    uint64_t str[3] = {cs, cs * W, cs * W * H};
+    uint32_t box[4] = {(uint32_t)A.BK, (uint32_t)A.BW, (uint32_t)(2 * A.BH + 2), 1};
+    rc = encode(&A.tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x.data, dims, str, box, one4, sw_in, "conv3 activations");
+    if (rc) { delete P; return rc; }
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)d.cin_pad, 9, (uint64_t)d.cout_pad};
+    uint64_t str[2] = {(uint64_t)d.cin_pad * 2, (uint64_t)d.cin_pad * 2 * 9};
+    uint32_t box[3] = {(uint32_t)A.BK, 1, (uint32_t)A.BN};
+    rc = encode(&A.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, d.weight, dims, str, box, one4, sw_in, "conv3 weights");
+    if (rc) { delete P; return rc; }
+  }
+  {
+    const uint64_t cs = (uint64_t)y.c_stride * 2;
+    uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)W, (uint64_t)H, (uint64_t)x.N};
+    uint64_t str[3] = {cs, cs * W, cs * W * H};
+    uint32_t box[4] = {64, (uint32_t)A.BW, (uint32_t)A.BH, 1};
+    rc = encode(&A.tm_y, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, y.data, dims, str, box, one4, CU_TENSOR_MAP_SWIZZLE_128B,
+                "conv3 output");
+    if (rc) { delete P; return rc; }
+  }
+  const long long total = (long long)A.tiles_n * A.tiles_w * A.tiles_h * x.N;
+  A.total_tiles = (int)total;
+  P->grid = (int)(total < num_sms() ? total : num_sms());
+  *out = P;
+  return YB_OK;
+}
+
+int conv3_tc_launch(const Conv3Plan* P, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    YB_CUDA(cudaFuncSetAttribute(k_conv3_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  k_conv3_tc<<<P->grid, kTcThreads, P->smem, s>>>(P->args);
+  YB_LAUNCH_CHECK();
+  return YB_OK;
+}
+
+void conv3_tc_plan_destroy(Conv3Plan* p) { delete p; }
+
+}  // namespace yb

@@ -13,9 +13,7 @@
 // (tcgen05.ld -> +bias -> SiLU/LeakyReLU -> bf16/fp32 -> swizzled smem -> TMA store).  The store
 // tensor map addresses a channel slice of the consumer's concat buffer (Concat fused away) and, for
 // convs feeding nn.Upsample, four maps with doubled strides write the 2x2 replicas.
-#include <cuda.h>
-
-#include "common.cuh"
+#include "tc_common.cuh"
 
 namespace yb {
 
@@ -40,103 +38,6 @@ struct ConvTcArgs {
   uint32_t idesc;
 };
 
-// ------------------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra WAIT_DONE;\n\t"
-      "bra WAIT_LOOP;\n\t"
-      "WAIT_DONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tma_load_4d(const CUtensorMap* tm, uint32_t bar, uint32_t dst, int c0, int c1, int c2,
-                                            int c3) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-}
-__device__ __forceinline__ void tma_load_3d(const CUtensorMap* tm, uint32_t bar, uint32_t dst, int c0, int c1, int c2) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
-}
-__device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src, int c0, int c1, int c2, int c3) {
-  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
-               ::"l"(tm), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// K-major shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout):
-//   [0,14) start>>4 | [16,30) LBO>>4 | [32,46) SBO>>4 | [46,48) version=1 | [61,64) layout type
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t sbo_bytes, uint32_t layout_type) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)(layout_type & 7) << 61;
-  return d;
-}
-
-__device__ __forceinline__ float act_fast(float v, int act, float slope) {
-  if (act == YB_ACT_SILU) return __fdividef(v, 1.0f + __expf(-v));
-  if (act == YB_ACT_LEAKY) return v > 0.f ? v : v * slope;
-  return v;
-}
-
-constexpr int kEpiWarps = 8;                       // two warps per TMEM lane quarter, each takes half the columns
-constexpr int kTcThreads = 64 + 32 * kEpiWarps;    // warp 0 producer, warp 1 MMA, warps 2.. epilogue
-constexpr int kMaxBias = 2048;
-
-// SiLU with ONE MUFU op per element: x*sigmoid(x) = 0.5x*tanh(0.5x) + 0.5x (tanh.approx rel. err ~2^-11 << bf16 ulp)
-__device__ __forceinline__ float silu_fast(float v) {
-  const float h = 0.5f * v;
-  float t;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
-  return fmaf(h, t, h);
-}
-__device__ __forceinline__ float act_epi(float v, int act, float slope) {
-  if (act == YB_ACT_SILU) return silu_fast(v);
-  if (act == YB_ACT_LEAKY) return v > 0.f ? v : v * slope;
-  return v;
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-
 // Persistent kernel: one CTA per SM walks tiles t = blockIdx.x, +gridDim.x, ...  The TMA producer runs
 // ahead across tile boundaries (smem ring of `stages` K-chunks), accumulators are double-buffered in
 // TMEM so the MMA of tile i+1 overlaps the epilogue of tile i, and the epilogue owns a dedicated
@@ -153,7 +54,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   const uint32_t out_es = G.out_f32 ? 4u : 2u;
   const uint32_t pipe_bytes = stage_bytes * G.stages;
   const uint32_t staging = tiles + pipe_bytes;                       // 1024-aligned (stage_bytes % 1024 == 0)
-  const uint32_t staging_bytes = 128u * G.BN * out_es;
+  const uint32_t staging_bytes = ((uint32_t)G.BN * out_es + 127u) / 128u * 16384u;   // 128 rows x 128 B per group
   unsigned char* aux = tiles_ptr + pipe_bytes + staging_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(aux);  // full[S], empty[S], tmem_full[2], tmem_empty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux + 8 * (2 * G.stages + 4));
@@ -184,59 +85,71 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
-      const uint32_t tx = (uint32_t)(G.BW * G.BH) * G.BK * 2u + b_bytes;
-      uint32_t kc = 0;  // running chunk counter across tiles -> ring slot + phase
-      for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x) {
-        const int n_tile = t % G.tiles_n;
-        int m_tile = t / G.tiles_n;
-        const int img = m_tile / tiles_m_per_img;
-        m_tile -= img * tiles_m_per_img;
-        const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
-        const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
-        for (int tap = 0; tap < G.taps; ++tap) {
-          const int dy = tap / G.ksz, dx = tap - dy * G.ksz;
-          const int cw = w0 * G.stride + dx - G.pad;
-          const int chh = G.flat ? 0 : h0 * G.stride + dy - G.pad;
-          for (int kk = 0; kk < G.kchunks; ++kk, ++kc) {
-            const uint32_t s = kc % (uint32_t)G.stages;
-            const uint32_t ph = (kc / (uint32_t)G.stages) & 1u;
-            mbar_wait(bar_empty0 + 8u * s, ph ^ 1u);
+    // Warp-uniform control flow, one elected lane issues the copies (coordinates live in uniform registers).
+    const uint32_t tx = (uint32_t)(G.BW * G.BH) * G.BK * 2u + b_bytes;
+    uint32_t s = 0, ph = 1;  // ring slot + parity to wait for on its empty barrier
+    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x) {
+      const int n_tile = t % G.tiles_n;
+      int m_tile = t / G.tiles_n;
+      const int img = m_tile / tiles_m_per_img;
+      m_tile -= img * tiles_m_per_img;
+      const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+      const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
+      int dy = 0, dx = 0;
+      for (int tap = 0; tap < G.taps; ++tap) {
+        const int cw = w0 * G.stride + dx - G.pad;
+        const int chh = G.flat ? 0 : h0 * G.stride + dy - G.pad;
+        for (int kk = 0; kk < G.kchunks; ++kk) {
+          mbar_wait(bar_empty0 + 8u * s, ph);
+          if (elect_one()) {
             const uint32_t full = bar_full0 + 8u * s;
             mbar_expect_tx(full, tx);
             const uint32_t sa = tiles + s * stage_bytes;
             tma_load_4d(&G.tm_a, full, sa, kk * G.BK, cw, chh, img);
             tma_load_3d(&G.tm_b, full, sa + a_bytes, kk * G.BK, tap, n0);
           }
+          __syncwarp();
+          if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
         }
+        if (++dx == G.ksz) { dx = 0; ++dy; }
       }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ==================================
-    if (lane == 0) {
-      const uint32_t sbo = 8u * (uint32_t)G.BK * 2u;
-      const int nk = G.BK / 16;
-      uint32_t kc = 0;
-      int it = 0;
-      for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
-        const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
-        mbar_wait(bar_tempty0 + 8u * acc, aph ^ 1u);       // epilogue has drained this accumulator
+    // Whole warp runs the (uniform) control flow; one elected lane issues tcgen05.mma / commit.
+    const uint32_t sbo = 8u * (uint32_t)G.BK * 2u;
+    const int nk = G.BK / 16;
+    const uint32_t hi32 = (uint32_t)(make_smem_desc(0, sbo, (uint32_t)G.sw_mode) >> 32);
+    const uint32_t boff = a_bytes >> 4;
+    uint32_t s = 0, ph = 0;
+    int it = 0;
+    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
+      const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
+      mbar_wait(bar_tempty0 + 8u * acc, aph ^ 1u);       // epilogue has drained this accumulator
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t tmem_d = tmem_base + acc * (uint32_t)G.BN;
+      for (int c = 0; c < total_chunks; ++c) {
+        mbar_wait(bar_full0 + 8u * s, ph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t tmem_d = tmem_base + acc * (uint32_t)G.BN;
-        for (int c = 0; c < total_chunks; ++c, ++kc) {
-          const uint32_t s = kc % (uint32_t)G.stages;
-          const uint32_t ph = (kc / (uint32_t)G.stages) & 1u;
-          mbar_wait(bar_full0 + 8u * s, ph);
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t sa = tiles + s * stage_bytes;
-          const uint64_t da = make_smem_desc(sa, sbo, (uint32_t)G.sw_mode);
-          const uint64_t db = make_smem_desc(sa + a_bytes, sbo, (uint32_t)G.sw_mode);
-          for (int k = 0; k < nk; ++k)
-            umma_bf16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), G.idesc, (uint32_t)((c | k) != 0));
-          umma_commit(bar_empty0 + 8u * s);
+        const uint32_t da = ((tiles + s * stage_bytes) >> 4) & 0x3FFF;
+        if (elect_one()) {
+          const uint32_t acc0 = (uint32_t)(c != 0);
+          if (nk == 4) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16_lh(tmem_d, da + 2u * k, da + boff + 2u * k, hi32, G.idesc, k ? 1u : acc0);
+          } else if (nk == 2) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) umma_bf16_lh(tmem_d, da + 2u * k, da + boff + 2u * k, hi32, G.idesc, k ? 1u : acc0);
+          } else {
+            umma_bf16_lh(tmem_d, da, da + boff, hi32, G.idesc, acc0);
+          }
+          umma_commit(bar_empty0 + 8u * s);   // frees the smem stage once these MMAs retire
         }
-        umma_commit(bar_tfull0 + 8u * acc);
+        __syncwarp();
+        if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
       }
+      if (elect_one()) umma_commit(bar_tfull0 + 8u * acc);
+      __syncwarp();
     }
   } else {
     // ================================ epilogue ====================================
@@ -315,46 +228,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G.tmem_cols)
                  : "memory");
   }
-}
-
-// ------------------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)p;
-  }
-  return fn;
-}
-
-static int encode(CUtensorMap* tm, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
-                  const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* estr, CUtensorMapSwizzle sw,
-                  const char* what) {
-  EncodeTiledFn fn = get_encode();
-  if (!fn) {
-    set_error("conv(tc): cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
-    return YB_ERR_CUDA;
-  }
-  cuuint64_t d[5], st[4];
-  cuuint32_t b[5], e[5];
-  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = estr[i]; }
-  for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
-  CUresult r = fn(tm, dt, (cuuint32_t)rank, const_cast<void*>(base), d, st, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_error("conv(tc): cuTensorMapEncodeTiled(%s) failed with %d (dims %llu,%llu,%llu,%llu box %u,%u,%u,%u)", what,
-              (int)r, (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)(rank > 2 ? dims[2] : 0),
-              (unsigned long long)(rank > 3 ? dims[3] : 0), box[0], box[1], rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
-    return YB_ERR_CUDA;
-  }
-  return YB_OK;
 }
 
 struct ConvTcPlan {
@@ -444,7 +317,7 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
   // stages / shared memory
   const size_t stage_bytes = (size_t)128 * A.BK * 2 + (size_t)A.BN * A.BK * 2;
-  const size_t stage_out = (size_t)128 * A.BN * y_es;
+  const size_t stage_out = ((size_t)A.BN * y_es + 127) / 128 * 16384;
   const size_t aux_bytes = 8 * (2 * 12 + 4) + 16 + (size_t)kMaxBias * 4 + 64;
   const size_t budget = 226 * 1024 - 1024 - stage_out - aux_bytes;
   int stages = d.stages ? d.stages : (int)(budget / stage_bytes);
@@ -550,8 +423,21 @@ extern "C" int yb_conv2d(const yb_conv_desc* d, void* stream) {
   YB_CHECK_ARG(d->y.H == Ho * d->upsample && d->y.W == Wo * d->upsample && d->y.N == d->x.N,
                "yb_conv2d: output dims must be (%d,%d)", Ho * d->upsample, Wo * d->upsample);
   if (d->x.dtype == YB_F32) return conv_fp32_launch(*d, (cudaStream_t)stream);
+  yb_conv_desc dd = *d;
+  if (dd.tile_n >= 0) {   // negative tile_n forces the generic kernel (tests / tuning)
+    Conv3Plan* p3 = nullptr;
+    int rc3 = conv3_tc_plan_create(dd, &p3);
+    if (rc3 == YB_OK) {
+      rc3 = conv3_tc_launch(p3, (cudaStream_t)stream);
+      conv3_tc_plan_destroy(p3);
+      return rc3;
+    }
+    if (rc3 != YB_ERR_UNSUPPORTED) return rc3;
+  } else {
+    dd.tile_n = dd.tile_n == -1 ? 0 : -dd.tile_n;
+  }
   ConvTcPlan* p = nullptr;
-  int rc = conv_tc_plan_create(*d, &p);
+  int rc = conv_tc_plan_create(dd, &p);
   if (rc) return rc;
   rc = conv_tc_launch(p, (cudaStream_t)stream);
   conv_tc_plan_destroy(p);

@@ -13,6 +13,7 @@ struct yb_engine {
   std::vector<const void*> weights;
   std::vector<const float*> biases;
   std::vector<yb::ConvTcPlan*> plans;  // per op (nullptr unless bf16 conv)
+  std::vector<yb::Conv3Plan*> plans3;  // per op (3x3 s1 slab kernel), takes precedence
   cudaGraphExec_t graph_exec = nullptr;
   cudaStream_t capture_stream = nullptr;
   int launches = 0;
@@ -29,7 +30,9 @@ static int run_ops(yb_engine* e, cudaStream_t s, cudaEvent_t* evs = nullptr) {
     int rc = YB_OK;
     switch (o.kind) {
       case YB_OP_CONV: {
-        if (e->plans[i]) {
+        if (e->plans3[i]) {
+          rc = conv3_tc_launch(e->plans3[i], s);
+        } else if (e->plans[i]) {
           rc = conv_tc_launch(e->plans[i], s);
         } else {
           yb_conv_desc d;
@@ -80,6 +83,7 @@ extern "C" int yb_engine_create(const yb_tensor* tensors, int n_tensors, const y
     e->biases.assign(biases, biases + n_weights);
   }
   e->plans.assign(n_ops, nullptr);
+  e->plans3.assign(n_ops, nullptr);
   for (int i = 0; i < n_ops; ++i) {
     const yb_op& o = e->ops[i];
     auto ok = [&](int idx) { return idx >= -1 && idx < n_tensors; };
@@ -101,7 +105,11 @@ extern "C" int yb_engine_create(const yb_tensor* tensors, int n_tensors, const y
     d.weight = e->weights[o.weight]; d.bias = e->biases[o.weight];
     d.cin_pad = o.cin_pad; d.cout_pad = o.cout_pad; d.k = o.k; d.stride = o.stride; d.act = o.act;
     d.leaky_slope = o.leaky_slope; d.upsample = o.upsample; d.tile_n = o.tile_n; d.stages = o.stages;
-    int rc = conv_tc_plan_create(d, &e->plans[i]);
+    int rc = d.tile_n < 0 ? YB_ERR_UNSUPPORTED : conv3_tc_plan_create(d, &e->plans3[i]);
+    if (rc == YB_ERR_UNSUPPORTED) {
+      if (d.tile_n < 0) d.tile_n = -d.tile_n == 1 ? 0 : -d.tile_n;   // negative tile_n forces the generic kernel
+      rc = conv_tc_plan_create(d, &e->plans[i]);
+    }
     if (rc) { yb_engine_destroy(e); return rc; }
   }
   *out = e;
@@ -153,6 +161,7 @@ extern "C" int yb_engine_num_launches(const yb_engine* e) { return e ? e->launch
 extern "C" void yb_engine_destroy(yb_engine* e) {
   if (!e) return;
   for (auto* p : e->plans) conv_tc_plan_destroy(p);
+  for (auto* p : e->plans3) conv3_tc_plan_destroy(p);
   if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
   if (e->capture_stream) cudaStreamDestroy(e->capture_stream);
   delete e;
