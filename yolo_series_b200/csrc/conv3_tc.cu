@@ -181,27 +181,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
         if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging free again
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (par * 2u + (uint32_t)j) * (uint32_t)G.BN;
-        for (int cc = c_begin; cc < c_end; ++cc) {
-          uint32_t v[32];
-          tmem_ld32(taddr + (uint32_t)(cc * 32), v);
-          const float* bs = bias_s + n0 + cc * 32;
-          const uint32_t base = staging + (uint32_t)(cc >> 1) * 16384u + (uint32_t)row * 128u;
-#pragma unroll
-          for (int jj = 0; jj < 4; ++jj) {
-            uint32_t p[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int i0 = 8 * jj + 2 * e;
-              const float f0 = act_epi(__uint_as_float(v[i0]) + bs[i0], G.act, G.slope);
-              const float f1 = act_epi(__uint_as_float(v[i0 + 1]) + bs[i0 + 1], G.act, G.slope);
-              __nv_bfloat162 hh = __floats2bfloat162_rn(f0, f1);
-              p[e] = *reinterpret_cast<uint32_t*>(&hh);
-            }
-            const uint32_t addr = base + ((((uint32_t)((cc & 1) * 4 + jj)) ^ xr) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(p[0]), "r"(p[1]), "r"(p[2]),
-                         "r"(p[3]) : "memory");
-          }
-        }
+        epi_chunks_dispatch(G.act, taddr, c_begin, c_end, bias_s + n0, G.slope, staging, row, xr, false);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");

@@ -176,37 +176,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
       if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging free again
       asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)G.BN;
-      for (int cc = c_begin; cc < c_end; ++cc) {
-        uint32_t v[32];
-        tmem_ld32(taddr + (uint32_t)(cc * 32), v);
-        float f[32];
-        const float* bs = bias_s + n0 + cc * 32;
-#pragma unroll
-        for (int i = 0; i < 32; ++i) f[i] = act_epi(__uint_as_float(v[i]) + bs[i], G.act, G.slope);
-        if (G.out_f32) {
-          const uint32_t base = staging + (uint32_t)cc * 16384u + (uint32_t)row * 128u;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t addr = base + ((((uint32_t)j) ^ xr) << 4);
-            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(f[4 * j]), "f"(f[4 * j + 1]),
-                         "f"(f[4 * j + 2]), "f"(f[4 * j + 3]) : "memory");
-          }
-        } else {
-          const uint32_t base = staging + (uint32_t)(cc >> 1) * 16384u + (uint32_t)row * 128u;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint32_t p[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              __nv_bfloat162 hh = __floats2bfloat162_rn(f[8 * j + 2 * e], f[8 * j + 2 * e + 1]);
-              p[e] = *reinterpret_cast<uint32_t*>(&hh);
-            }
-            const uint32_t addr = base + ((((uint32_t)((cc & 1) * 4 + j)) ^ xr) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(p[0]), "r"(p[1]), "r"(p[2]),
-                         "r"(p[3]) : "memory");
-          }
-        }
-      }
+      epi_chunks_dispatch(G.act, taddr, c_begin, c_end, bias_s + n0, G.slope, staging, row, xr, G.out_f32 != 0);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to TMA
       asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");

@@ -112,6 +112,74 @@ __device__ __forceinline__ float act_epi(float v, int act, float slope) {
   if (act == YB_ACT_LEAKY) return v > 0.f ? v : v * slope;
   return v;
 }
+// ---- epilogue: one 32-column TMEM chunk of one accumulator row -> bias + activation -> swizzled staging.
+// ACT is a template parameter so the 32 elements form one straight-line block (a per-element runtime
+// switch serialises the LDS -> FADD -> MUFU chains); the bias is read with 8 LDS.128.
+template <int ACT>
+__device__ __forceinline__ void epi_bias_act(const uint32_t (&v)[32], const float* bs, float slope, float (&f)[32]) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float4 b = reinterpret_cast<const float4*>(bs)[j];
+    const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float x = __uint_as_float(v[4 * j + e]) + bb[e];
+      f[4 * j + e] = ACT == YB_ACT_SILU ? silu_fast(x) : ACT == YB_ACT_LEAKY ? (x > 0.f ? x : x * slope) : x;
+    }
+  }
+}
+// bf16 output: the chunk is half (sub = 0/1) of a 128-byte staging row (64 channels), SW128 pattern.
+template <int ACT>
+__device__ __forceinline__ void epi_chunk_bf16(const uint32_t (&v)[32], const float* bs, float slope, uint32_t row_base,
+                                               uint32_t sub, uint32_t xr) {
+  float f[32];
+  epi_bias_act<ACT>(v, bs, slope, f);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t p[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      __nv_bfloat162 hh = __floats2bfloat162_rn(f[8 * j + 2 * e], f[8 * j + 2 * e + 1]);
+      p[e] = *reinterpret_cast<uint32_t*>(&hh);
+    }
+    const uint32_t addr = row_base + (((sub * 4u + (uint32_t)j) ^ xr) << 4);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(p[0]), "r"(p[1]), "r"(p[2]), "r"(p[3])
+                 : "memory");
+  }
+}
+// fp32 output: the chunk is a whole 128-byte staging row (32 channels).
+template <int ACT>
+__device__ __forceinline__ void epi_chunk_f32(const uint32_t (&v)[32], const float* bs, float slope, uint32_t row_base,
+                                              uint32_t xr) {
+  float f[32];
+  epi_bias_act<ACT>(v, bs, slope, f);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t addr = row_base + ((((uint32_t)j) ^ xr) << 4);
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(f[4 * j]), "f"(f[4 * j + 1]),
+                 "f"(f[4 * j + 2]), "f"(f[4 * j + 3]) : "memory");
+  }
+}
+// All chunks [c_begin, c_end) of one accumulator for this warp.
+template <int ACT>
+__device__ __forceinline__ void epi_chunks(uint32_t taddr, int c_begin, int c_end, const float* bias_n0, float slope,
+                                           uint32_t staging, int row, uint32_t xr, bool out_f32) {
+  for (int cc = c_begin; cc < c_end; ++cc) {
+    uint32_t v[32];
+    tmem_ld32(taddr + (uint32_t)(cc * 32), v);
+    const float* bs = bias_n0 + cc * 32;
+    if (out_f32) epi_chunk_f32<ACT>(v, bs, slope, staging + (uint32_t)cc * 16384u + (uint32_t)row * 128u, xr);
+    else epi_chunk_bf16<ACT>(v, bs, slope, staging + (uint32_t)(cc >> 1) * 16384u + (uint32_t)row * 128u,
+                             (uint32_t)(cc & 1), xr);
+  }
+}
+__device__ __forceinline__ void epi_chunks_dispatch(int act, uint32_t taddr, int c_begin, int c_end, const float* bias_n0,
+                                                    float slope, uint32_t staging, int row, uint32_t xr, bool out_f32) {
+  if (act == YB_ACT_SILU) epi_chunks<YB_ACT_SILU>(taddr, c_begin, c_end, bias_n0, slope, staging, row, xr, out_f32);
+  else if (act == YB_ACT_LEAKY) epi_chunks<YB_ACT_LEAKY>(taddr, c_begin, c_end, bias_n0, slope, staging, row, xr, out_f32);
+  else epi_chunks<YB_ACT_NONE>(taddr, c_begin, c_end, bias_n0, slope, staging, row, xr, out_f32);
+}
+
 // One elected lane of a fully converged warp.  The surrounding control flow stays warp-uniform, so
 // descriptor / address arithmetic is done once on the uniform datapath instead of per MMA via R2UR.
 __device__ __forceinline__ bool elect_one() {
