@@ -82,4 +82,8 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out);
 int conv3_tc_launch(const Conv3Plan* p, cudaStream_t s);
 void conv3_tc_plan_destroy(Conv3Plan* p);
 
+// tcgen05 first layer for 3-channel images (stem_tc.cu); YB_ERR_UNSUPPORTED -> caller uses the mma.sync stem
+int stem_tc_launch(const void* img, int img_u8, int B, int H, int W, const void* weight, const float* bias,
+                   int cin_pad, int stride, int act, float slope, const yb_tensor* y, cudaStream_t st);
+
 }  // namespace yb

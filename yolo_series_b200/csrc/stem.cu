@@ -261,10 +261,13 @@ extern "C" int yb_stem_conv(const void* img, int img_dtype, int B, int C, int H,
   P.KD = (3 * P.CP + 15) / 16 * 16;
   P.tiles_w = (P.Wo + kStemTile - 1) / kStemTile;
   cudaStream_t st = (cudaStream_t)stream;
-  const bool fast3 = !reorg && C == 3 && W % 4 == 0 && (uintptr_t)img % 16 == 0;
+  if (!reorg && C == 3) {   // plain RGB first layer: tcgen05 kernel (stem_tc.cu)
+    const int rc = stem_tc_launch(img, P.img_u8, B, H, W, weight, bias, cin_pad, stride, act, leaky_slope, y, st);
+    if (rc != YB_ERR_UNSUPPORTED) return rc;
+  }
   const int nt = P.Cout / 16;
-  if (P.CP == 8 && stride == 1 && nt == 2) return fast3 ? launch_stem<2, 8, 1, true>(P, st) : launch_stem<2, 8, 1, false>(P, st);
-  if (P.CP == 8 && stride == 2 && nt == 2) return fast3 ? launch_stem<2, 8, 2, true>(P, st) : launch_stem<2, 8, 2, false>(P, st);
+  if (P.CP == 8 && stride == 1 && nt == 2) return launch_stem<2, 8, 1, false>(P, st);
+  if (P.CP == 8 && stride == 2 && nt == 2) return launch_stem<2, 8, 2, false>(P, st);
   if (P.CP == 16 && stride == 1 && nt == 4) return launch_stem<4, 16, 1, false>(P, st);
   if (P.CP == 16 && stride == 1 && nt == 5) return launch_stem<5, 16, 1, false>(P, st);
   set_error("yb_stem_conv: no specialisation for Cin=%d Cout=%d stride=%d (supported: 3->32 s1|s2, 12->64, 12->80)", P.Cin,
