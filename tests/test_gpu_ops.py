@@ -125,9 +125,10 @@ def test_stage_input_and_reorg():
 
 @pytest.mark.parametrize('cfg', [(3, 32, 1, False, 48, 160), (3, 32, 2, False, 64, 200), (3, 64, 1, True, 64, 96),
                                  (3, 80, 1, True, 32, 288), (3, 32, 1, False, 37, 70), (3, 32, 2, False, 45, 75),
-                                 (3, 32, 1, False, 256, 320), (3, 32, 2, False, 256, 640)],
+                                 (3, 32, 1, False, 256, 320), (3, 32, 2, False, 256, 640), (3, 32, 1, False, 37, 72),
+                                 (3, 32, 2, False, 45, 76)],
                          ids=['v7', 'tiny_s2', 'w6_reorg', 'e6e_reorg', 'v7_ragged', 'tiny_ragged', 'v7_ringwrap',
-                              'tiny_ringwrap'])
+                              'tiny_ringwrap', 'v7_ragged4', 'tiny_ragged4'])
 @pytest.mark.parametrize('u8', [True, False])
 def test_stem_conv_fused_staging(cfg, u8):
     """Fused staging + first conv (tcgen05 kernel for RGB -> 32, mma.sync kernel for the ReOrg stems) vs fp32
