@@ -1,0 +1,7 @@
+#!/bin/bash
+# ncu launch list (gpu__time_duration per kernel launch) of bench.py's step, as profiles/ wants it.
+mkdir -p gpurun_out
+python bench.py --steps 2 --warmup 1 --no-extras > gpurun_out/ll_plain.json 2> gpurun_out/ll_plain.err || { echo plain failed; tail -3 gpurun_out/ll_plain.err; exit 1; }
+ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/launches.csv \
+  python bench.py --steps 2 --warmup 1 --no-extras > gpurun_out/ll_ncu.log 2>&1
+echo "ncu rc=$?"; wc -l gpurun_out/launches.csv

@@ -8,7 +8,7 @@
 namespace yb {
 
 __device__ __forceinline__ float sigmoid_rn(float t) {
-  return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-t)));
+  return __frcp_rn(__fadd_rn(1.0f, expf(-t)));   // == __fdiv_rn(1, x): both correctly rounded
 }
 
 __device__ __forceinline__ float decode_elem(float p, int o, int gx, int gy, float stride, float aw, float ah) {

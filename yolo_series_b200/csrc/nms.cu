@@ -24,6 +24,7 @@ struct HeadLevelDev {  // fused decode source (yb_decode_nms)
   float stride;
   float anchor_wh[2 * YB_MAX_ANCHORS];
   int row_off;
+  unsigned magic_cells, magic_nx;   // floor(2^32 / d) + 1 for d = ny*nx and d = nx
 };
 
 struct FilterParams {
@@ -37,6 +38,7 @@ struct FilterParams {
   int multi_label, use_class_mask;
   uint32_t class_mask[kMaxClassWords];
   int cap;
+  int rows_per_block, blocks_per_img;   // launch geometry: grid = B * blocks_per_img
   // outputs
   int* count;            // [B]
   uint64_t* keys;        // [B][cap]
@@ -45,115 +47,137 @@ struct FilterParams {
   int* overflow;         // nullable
 };
 
-__device__ __forceinline__ float sigmoid_rn_(float t) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-t))); }
+// __frcp_rn(x) and __fdiv_rn(1, x) are both the correctly rounded 1/x, i.e. the same float; the former is cheaper.
+__device__ __forceinline__ float sigmoid_rn_(float t) { return __frcp_rn(__fadd_rn(1.0f, expf(-t))); }
 
 __device__ __forceinline__ bool class_allowed(const FilterParams& P, int c) {
   return !P.use_class_mask || ((P.class_mask[c >> 5] >> (c & 31)) & 1u);
 }
 
-// One warp per row.  Lane l holds channels l, l+32, l+64, ... of the row.
-template <bool FUSED, typename TL>
+// One warp per row; lane l holds channels l, l+32, l+64, ... of the row.  A block owns a contiguous run of rows
+// of ONE image and collects its candidate keys in shared memory, so the per-image counter sees one atomicAdd per
+// batch instead of one per candidate row (25 200 same-address atomics per image serialise in L2 otherwise).
+// Slot order inside an image is arbitrary: every key is distinct (it carries the row index) and k_sort_nms
+// sorts them, so the result does not depend on it.
+constexpr int kFilterBuf = 2048;   // keys buffered per block between flushes
+
+// NV = number of 32-channel groups a row spans (compile-time so that the per-group code is not predicated 8 ways).
+template <bool FUSED, typename TL, int NV>
 __global__ void __launch_bounds__(256) k_filter(const FilterParams P) {
-  const int lane = threadIdx.x & 31;
-  const size_t warp0 = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
-  const size_t nwarps = ((size_t)gridDim.x * blockDim.x) >> 5;
-  const size_t rows = (size_t)P.B * P.A;
-  constexpr int MAXV = 8;  // supports no <= 256 per row per warp-iteration chunking below
-  for (size_t r = warp0; r < rows; r += nwarps) {
-    const int b = (int)(r / P.A), row = (int)(r % P.A);
-    // ---- locate the row
-    const float* src = nullptr;
-    const TL* lsrc = nullptr;
-    float stride = 0.f, aw = 0.f, ah = 0.f;
-    int gx = 0, gy = 0;
-    if (!FUSED) {
-      src = P.pred + r * P.no;
-    } else {
-      int l = 0;
-      while (l + 1 < P.nl && row >= P.lv[l + 1].row_off) ++l;
-      const HeadLevelDev& L = P.lv[l];
-      int cell = row - L.row_off;
-      int a = cell / (L.ny * L.nx);
-      int rem = cell - a * L.ny * L.nx;
-      gy = rem / L.nx; gx = rem - gy * L.nx;
-      lsrc = reinterpret_cast<const TL*>(L.logits) + (((size_t)b * L.ny + gy) * L.nx + gx) * L.c_stride + a * P.no;
-      stride = L.stride; aw = L.anchor_wh[2 * a]; ah = L.anchor_wh[2 * a + 1];
-    }
-    // ---- first 32 channels: box + obj (+27 classes)
-    float v0 = 0.f;
-    if (lane < P.no) v0 = FUSED ? sigmoid_rn_(Elem<TL>::load(lsrc + lane)) : __ldg(src + lane);
-    const float obj = __shfl_sync(0xffffffffu, v0, 4);
-    if (!(obj > P.conf_thres)) continue;  // general.py:637,653
-    // xywh (decoded when fused)
-    float bx = __shfl_sync(0xffffffffu, v0, 0), by = __shfl_sync(0xffffffffu, v0, 1);
-    float bw = __shfl_sync(0xffffffffu, v0, 2), bh = __shfl_sync(0xffffffffu, v0, 3);
-    if (FUSED) {
-      bx = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(bx, 2.f), 0.5f), (float)gx), stride);
-      by = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(by, 2.f), 0.5f), (float)gy), stride);
-      float w2 = __fmul_rn(bw, 2.f), h2 = __fmul_rn(bh, 2.f);
-      bw = __fmul_rn(__fmul_rn(w2, w2), aw);
-      bh = __fmul_rn(__fmul_rn(h2, h2), ah);
-    }
-    // ---- class confidences: conf_c = cls_c * obj (general.py:673); nc == 1: conf = obj (:670)
-    float best = -INFINITY;
-    int best_c = 0x7fffffff;
-    int n_emit_total = 0;
-    for (int it = 0; it < MAXV && it * 32 < P.no; ++it) {
-      const int ch = it * 32 + lane;
-      float v = v0;
-      if (it > 0) {
-        v = 0.f;
-        if (ch < P.no) v = FUSED ? sigmoid_rn_(Elem<TL>::load(lsrc + ch)) : __ldg(src + ch);
-      }
-      const int c = ch - 5;
-      const bool is_cls = (c >= 0) && (ch < P.no);
-      float conf = (P.nc == 1) ? obj : __fmul_rn(v, obj);
-      if (!P.multi_label) {
-        if (is_cls && (conf > best)) { best = conf; best_c = c; }  // strict > keeps the first index in-lane
+  __shared__ uint64_t kbuf[kFilterBuf];
+  __shared__ int s_n, s_base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.x / P.blocks_per_img, blk = blockIdx.x - b * P.blocks_per_img;
+  const int row_begin = blk * P.rows_per_block;
+  const int row_end = min(P.A, row_begin + P.rows_per_block);
+  const int batch_rows = P.multi_label ? kFilterBuf / P.nc : kFilterBuf;   // worst case fills the buffer exactly
+  constexpr int MAXV = NV;  // no <= 32 * NV channels
+  if (threadIdx.x == 0) s_n = 0;
+  __syncthreads();
+  for (int batch0 = row_begin; batch0 < row_end; batch0 += batch_rows) {
+    const int batch1 = min(row_end, batch0 + batch_rows);
+    for (int row = batch0 + warp; row < batch1; row += 8) {
+      // ---- locate the row
+      const float* src = nullptr;
+      const TL* lsrc = nullptr;
+      float stride = 0.f, aw = 0.f, ah = 0.f;
+      int gx = 0, gy = 0;
+      if (!FUSED) {
+        src = P.pred + ((size_t)b * P.A + row) * P.no;
       } else {
-        const bool emit = is_cls && (conf > P.conf_thres) && class_allowed(P, c);
-        const unsigned m = __ballot_sync(0xffffffffu, emit);
-        if (m) {
-          int base = 0;
-          const int cnt = __popc(m);
-          if (lane == 0) base = atomicAdd(P.count + b, cnt);
-          base = __shfl_sync(0xffffffffu, base, 0);
-          if (emit) {
-            const int slot = base + __popc(m & ((1u << lane) - 1u));
-            if (slot < P.cap) {
-              const uint32_t idx = (uint32_t)row * (uint32_t)P.nc + (uint32_t)c;
-              P.keys[(size_t)b * P.cap + slot] = ((uint64_t)(~__float_as_uint(conf)) << 32) | idx;
-            } else if (P.overflow) {
-              *P.overflow = 1;
-            }
-          }
-          n_emit_total += cnt;
-        }
+        int l = 0;
+        while (l + 1 < P.nl && row >= P.lv[l + 1].row_off) ++l;
+        const HeadLevelDev& L = P.lv[l];
+        const int cell = row - L.row_off;
+        // cell / (ny*nx) and rem / nx by multiplication (exact for n*d < 2^32; d == 1 has no 32-bit magic)
+        const int a = L.magic_cells ? (int)__umulhi((unsigned)cell, L.magic_cells) : cell;
+        const int rem = cell - a * L.ny * L.nx;
+        gy = L.magic_nx ? (int)__umulhi((unsigned)rem, L.magic_nx) : rem; gx = rem - gy * L.nx;
+        lsrc = reinterpret_cast<const TL*>(L.logits) + (((size_t)b * L.ny + gy) * L.nx + gx) * L.c_stride + a * P.no;
+        stride = L.stride; aw = L.anchor_wh[2 * a]; ah = L.anchor_wh[2 * a + 1];
       }
-    }
-    if (!P.multi_label) {
-      // warp argmax with first-index tie-break (torch.max returns the first maximal index)
+      // ---- all channels of the row up front (independent loads), then the arithmetic
+      float raw[MAXV];
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        float ob = __shfl_xor_sync(0xffffffffu, best, o);
-        int oc = __shfl_xor_sync(0xffffffffu, best_c, o);
-        if (ob > best || (ob == best && oc < best_c)) { best = ob; best_c = oc; }
+      for (int it = 0; it < MAXV; ++it) {
+        const int ch = it * 32 + lane;
+        raw[it] = 0.f;
+        if (ch < P.no) raw[it] = FUSED ? Elem<TL>::load(lsrc + ch) : __ldg(src + ch);
       }
-      if (lane == 0 && best > P.conf_thres && class_allowed(P, best_c)) {  // general.py:684,688
-        const int slot = atomicAdd(P.count + b, 1);
-        if (slot < P.cap) {
-          P.keys[(size_t)b * P.cap + slot] = ((uint64_t)(~__float_as_uint(best)) << 32) | (uint32_t)row;
-          P.cls_of_row[(size_t)b * P.A + row] = (uint16_t)best_c;
-        } else if (P.overflow) {
-          *P.overflow = 1;
+      const float v0 = FUSED ? sigmoid_rn_(raw[0]) : raw[0];
+      const float obj = __shfl_sync(0xffffffffu, v0, 4);
+      if (!(obj > P.conf_thres)) continue;  // general.py:637,653
+      // xywh (decoded when fused)
+      float bx = __shfl_sync(0xffffffffu, v0, 0), by = __shfl_sync(0xffffffffu, v0, 1);
+      float bw = __shfl_sync(0xffffffffu, v0, 2), bh = __shfl_sync(0xffffffffu, v0, 3);
+      if (FUSED) {
+        bx = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(bx, 2.f), 0.5f), (float)gx), stride);
+        by = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(by, 2.f), 0.5f), (float)gy), stride);
+        float w2 = __fmul_rn(bw, 2.f), h2 = __fmul_rn(bh, 2.f);
+        bw = __fmul_rn(__fmul_rn(w2, w2), aw);
+        bh = __fmul_rn(__fmul_rn(h2, h2), ah);
+      }
+      // ---- class confidences: conf_c = cls_c * obj (general.py:673); nc == 1: conf = obj (:670)
+      float best = -INFINITY;
+      int best_c = 0x7fffffff;
+      int n_emit_total = 0;
+#pragma unroll
+      for (int it = 0; it < MAXV; ++it) {
+        const int ch = it * 32 + lane;
+        const float v = it == 0 ? v0 : (FUSED ? sigmoid_rn_(raw[it]) : raw[it]);
+        const int c = ch - 5;
+        const bool is_cls = (c >= 0) && (ch < P.no);
+        const float conf = (P.nc == 1) ? obj : __fmul_rn(v, obj);
+        if (!P.multi_label) {
+          if (is_cls && (conf > best)) { best = conf; best_c = c; }  // strict > keeps the first index in-lane
+        } else {
+          const bool emit = is_cls && (conf > P.conf_thres) && class_allowed(P, c);
+          const unsigned m = __ballot_sync(0xffffffffu, emit);
+          if (m) {
+            int base = 0;
+            const int cnt = __popc(m);
+            if (lane == 0) base = atomicAdd(&s_n, cnt);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (emit) {
+              const uint32_t idx = (uint32_t)row * (uint32_t)P.nc + (uint32_t)c;
+              kbuf[base + __popc(m & ((1u << lane) - 1u))] = ((uint64_t)(~__float_as_uint(conf)) << 32) | idx;
+            }
+            n_emit_total += cnt;
+          }
         }
-        n_emit_total = 1;
       }
-      n_emit_total = __shfl_sync(0xffffffffu, n_emit_total, 0);
+      if (!P.multi_label) {
+        // warp argmax with first-index tie-break (torch.max returns the first maximal index)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          float ob = __shfl_xor_sync(0xffffffffu, best, o);
+          int oc = __shfl_xor_sync(0xffffffffu, best_c, o);
+          if (ob > best || (ob == best && oc < best_c)) { best = ob; best_c = oc; }
+        }
+        if (lane == 0 && best > P.conf_thres && class_allowed(P, best_c)) {  // general.py:684,688
+          kbuf[atomicAdd(&s_n, 1)] = ((uint64_t)(~__float_as_uint(best)) << 32) | (uint32_t)row;
+          P.cls_of_row[(size_t)b * P.A + row] = (uint16_t)best_c;
+          n_emit_total = 1;
+        }
+        n_emit_total = __shfl_sync(0xffffffffu, n_emit_total, 0);
+      }
+      if (FUSED && n_emit_total > 0 && lane == 0) {
+        *reinterpret_cast<float4*>(P.boxes + ((size_t)b * P.A + row) * 4) = make_float4(bx, by, bw, bh);
+      }
     }
-    if (FUSED && n_emit_total > 0 && lane == 0) {
-      *reinterpret_cast<float4*>(P.boxes + ((size_t)b * P.A + row) * 4) = make_float4(bx, by, bw, bh);
+    // ---- flush the batch: one global atomic, coalesced key stores
+    __syncthreads();
+    if (threadIdx.x == 0) s_base = s_n ? atomicAdd(P.count + b, s_n) : 0;
+    __syncthreads();
+    const int n = s_n, base = s_base;
+    for (int i = threadIdx.x; i < n; i += 256) {
+      const int slot = base + i;
+      if (slot < P.cap) P.keys[(size_t)b * P.cap + slot] = kbuf[i];
+      else if (P.overflow) *P.overflow = 1;
     }
+    __syncthreads();
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
   }
 }
 
@@ -457,12 +481,26 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
   YB_CUDA(cudaMemsetAsync(W.count, 0, (size_t)B * 4, s));
   if (overflow) YB_CUDA(cudaMemsetAsync(overflow, 0, 4, s));
   {
-    size_t rows = (size_t)B * A;
-    size_t g = (rows + 7) / 8, cap = (size_t)num_sms() * 8;
-    int grid = (int)(g < cap ? g : cap);
-    if (!fused) k_filter<false, float><<<grid, 256, 0, s>>>(F);
-    else if (logits_dtype == YB_F32) k_filter<true, float><<<grid, 256, 0, s>>>(F);
-    else k_filter<true, __nv_bfloat16><<<grid, 256, 0, s>>>(F);
+    // ~8 resident blocks per SM over the whole batch, at least 64 rows per block
+    int bpi = (num_sms() * 8 + B - 1) / B;
+    if (bpi > (A + 63) / 64) bpi = (A + 63) / 64;
+    if (bpi < 1) bpi = 1;
+    F.rows_per_block = (A + bpi - 1) / bpi;
+    F.blocks_per_img = (A + F.rows_per_block - 1) / F.rows_per_block;
+    const int grid = B * F.blocks_per_img;
+    const int nv = (F.no + 31) / 32;
+#define YB_FILTER_LAUNCH(NVV)                                                              \
+    do {                                                                                   \
+      if (!fused) k_filter<false, float, NVV><<<grid, 256, 0, s>>>(F);                     \
+      else if (logits_dtype == YB_F32) k_filter<true, float, NVV><<<grid, 256, 0, s>>>(F); \
+      else k_filter<true, __nv_bfloat16, NVV><<<grid, 256, 0, s>>>(F);                     \
+    } while (0)
+    if (nv <= 1) YB_FILTER_LAUNCH(1);
+    else if (nv == 2) YB_FILTER_LAUNCH(2);
+    else if (nv == 3) YB_FILTER_LAUNCH(3);
+    else if (nv == 4) YB_FILTER_LAUNCH(4);
+    else YB_FILTER_LAUNCH(8);
+#undef YB_FILTER_LAUNCH
     YB_LAUNCH_CHECK();
   }
   NmsParams N;
@@ -528,6 +566,9 @@ extern "C" int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no
     L.stride = levels[l].stride;
     memcpy(L.anchor_wh, levels[l].anchor_wh, sizeof(L.anchor_wh));
     L.row_off = A;
+    L.magic_cells = t.H * t.W > 1 ? (unsigned)(0x100000000ULL / (unsigned long long)(t.H * t.W)) + 1u : 0u;
+    L.magic_nx = t.W > 1 ? (unsigned)(0x100000000ULL / (unsigned long long)t.W) + 1u : 0u;
+    YB_CHECK_ARG((long long)na * t.H * t.W * t.H * t.W < 0x100000000LL, "yb_decode_nms: level %d too large", l);
     A += na * t.H * t.W;
   }
   F.nl = nl; F.na = na; F.B = B; F.A = A; F.no = no; F.nc = no - 5; F.conf_thres = conf_thres;
