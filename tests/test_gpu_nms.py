@@ -63,6 +63,33 @@ def test_nms_suppression_heavy_never_reaches_max_det():
     assert np.array_equal(_flat(out), _flat(ref))
 
 
+@pytest.mark.parametrize('mode', ['all_equal', 'few_levels', 'two_level_refine'])
+def test_nms_score_ties_across_bands(mode):
+    """The sort+NMS kernel takes candidates in score bands picked by a radix select; equal scores must still come
+    out in index order, whether the tie fits one band, spans the select's refinement levels or overflows a band
+    (more than 4096 equal scores -> full sort fallback)."""
+    from yolo_series_b200 import non_max_suppression
+    pred = synth_pred(2, 12000, 3, seed=21, p_obj=1.0, extent=2000.0)
+    g = torch.Generator().manual_seed(5)
+    if mode == 'all_equal':            # 12000 identical scores: one tie larger than a band
+        pred[..., 4] = 1.0
+        pred[..., 5:] = 0.5
+    elif mode == 'few_levels':         # 4 distinct scores, 3000 boxes each
+        pred[..., 4] = 1.0
+        lv = torch.tensor([0.9, 0.7, 0.5, 0.3])[torch.randint(0, 4, (2, 12000), generator=g)]
+        pred[..., 5:] = lv[..., None]
+    else:                              # scores differing only in the low mantissa bits
+        pred[..., 4] = 1.0
+        base = torch.tensor(0.75).view(torch.int32)
+        bits = base + torch.randint(0, 200, (2, 12000), generator=g, dtype=torch.int32)
+        pred[..., 5:] = bits.view(torch.float32)[..., None]
+    for kw in (dict(conf_thres=0.001, iou_thres=0.65, max_det=300), dict(conf_thres=0.001, iou_thres=0.2, max_det=3000)):
+        ref = non_max_suppression_ref(pred, **kw)
+        out = non_max_suppression(pred.cuda(), **kw)
+        assert [o.shape[0] for o in out] == [r.shape[0] for r in ref]
+        assert np.array_equal(_flat(out), _flat(ref))
+
+
 def test_nms_edge_cases():
     from yolo_series_b200 import non_max_suppression
     z = torch.zeros((2, 64, 85)).cuda()

@@ -220,92 +220,177 @@ __device__ __forceinline__ bool iou_suppresses(float ix1, float iy1, float ix2, 
   return ovr > thr_f;
 }
 
+// Candidates are consumed in bands of descending score: a band is picked by a radix select on the score bits
+// (at least kBandMin keys, at most kBandCap so that it sorts inside shared memory), sorted, and fed to the greedy
+// loop, which usually reaches max_det inside the first band.  Bands are disjoint key ranges taken in key order and
+// every key is distinct, so the sequence of candidates is exactly that of one full sort (general.py:695-699).
+constexpr int kBandMin = 1024;
+constexpr int kBandCap = 4096;
+
+// Stable LSD radix sort (8-bit digits) of n 64-bit keys by the whole block; src/dst may be shared or global.
+// Returns the buffer holding the sorted keys.  whist: [kSortWarps][256] ints of scratch.
+__device__ uint64_t* block_radix_sort(uint64_t* src, uint64_t* dst, int n, int* whist) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ unsigned long long s_and, s_or;
+  __shared__ int digit_tot[256];
+  __syncthreads();
+  if (tid == 0) { s_and = ~0ull; s_or = 0ull; }
+  __syncthreads();
+  unsigned long long a = ~0ull, o = 0ull;
+  for (int i = tid; i < n; i += kSortThreads) { unsigned long long k = src[i]; a &= k; o |= k; }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    a &= __shfl_xor_sync(0xffffffffu, a, s);
+    o |= __shfl_xor_sync(0xffffffffu, o, s);
+  }
+  if (lane == 0) { atomicAnd(&s_and, a); atomicOr(&s_or, o); }
+  __syncthreads();
+  const unsigned long long varying = s_and ^ s_or;
+  // contiguous segment of the array owned by each warp (keeps the scatter stable)
+  const int per_warp = ((n + kSortWarps - 1) / kSortWarps + 31) / 32 * 32;
+  const int seg0 = min(n, warp * per_warp), seg1 = min(n, seg0 + per_warp);
+  for (int pass = 0; pass < 8 && n > 1; ++pass) {
+    const int sh = pass * 8;
+    if (((varying >> sh) & 0xffull) == 0) continue;  // digit identical for every key
+    for (int i = tid; i < kSortWarps * 256; i += kSortThreads) whist[i] = 0;
+    __syncthreads();
+    int* myh = whist + warp * 256;
+    for (int i = seg0 + lane; i - lane < seg1; i += 32) {
+      const bool valid = i < seg1;
+      const int d = valid ? (int)((src[i] >> sh) & 0xff) : 256 + lane;  // unique dummy digit per idle lane
+      const unsigned peers = __match_any_sync(0xffffffffu, d);
+      if (valid && lane == __ffs(peers) - 1) myh[d] += __popc(peers);
+      __syncwarp();
+    }
+    __syncthreads();
+    // exclusive scan in (digit major, warp minor) order: thread t<256 owns digit t
+    if (tid < 256) {
+      int s = 0;
+      for (int w = 0; w < kSortWarps; ++w) { int c = whist[w * 256 + tid]; whist[w * 256 + tid] = s; s += c; }
+      digit_tot[tid] = s;
+    }
+    __syncthreads();
+    if (warp == 0) {  // scan the 256 digit totals
+      int carry = 0;
+      for (int base = 0; base < 256; base += 32) {
+        int v = digit_tot[base + lane], x = v;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, s); if (lane >= s) x += y; }
+        digit_tot[base + lane] = carry + x - v;
+        carry += __shfl_sync(0xffffffffu, x, 31);
+      }
+    }
+    __syncthreads();
+    if (tid < 256) {
+      const int base = digit_tot[tid];
+      for (int w = 0; w < kSortWarps; ++w) whist[w * 256 + tid] += base;
+    }
+    __syncthreads();
+    for (int i = seg0 + lane; i - lane < seg1; i += 32) {
+      const bool valid = i < seg1;
+      unsigned long long k = valid ? src[i] : 0ull;
+      const int d = valid ? (int)((k >> sh) & 0xff) : 256 + lane;
+      const unsigned peers = __match_any_sync(0xffffffffu, d);
+      int pos = 0;
+      if (valid) pos = myh[d] + __popc(peers & ((1u << lane) - 1u));
+      __syncwarp();
+      if (valid && lane == __ffs(peers) - 1) myh[d] += __popc(peers);
+      __syncwarp();
+      if (valid) dst[pos] = k;
+    }
+    __syncthreads();
+    uint64_t* t = src; src = dst; dst = t;
+  }
+  __syncthreads();
+  return src;
+}
+
+// Radix select on the high key word h = ~score_bits (ascending h = descending score): the smallest T such that
+// the keys with lo < h <= T (all keys with h <= T when !have_lo) number at least kBandMin -- refined over up to
+// three digit levels (12 + 12 + 8 bits) while that count exceeds kBandCap.  If fewer than kBandMin keys are left,
+// T = 0xffffffff takes them all.  Returns the band size through s_out[0] and T through s_out[1].
+// hist: 4096 ints of scratch.
+__device__ void select_band(const uint64_t* keys, int n, uint32_t lo, bool have_lo, int* hist, uint32_t* s_out) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ int s_wsum[kSortWarps];
+  __shared__ int s_found, s_bin, s_cum_in, s_cum_ex, s_total;
+  uint32_t prefix = 0;
+  int pbits = 0, below = 0;
+  for (int level = 0; level < 3; ++level) {
+    const int nb = level < 2 ? 12 : 8;
+    const int shift = level == 0 ? 20 : level == 1 ? 8 : 0;
+    const int nbins = 1 << nb;
+    __syncthreads();
+    for (int i = tid; i < nbins; i += kSortThreads) hist[i] = 0;
+    if (tid == 0) s_found = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += kSortThreads) {
+      const uint32_t h = (uint32_t)(keys[i] >> 32);
+      if (have_lo && h <= lo) continue;
+      if (pbits && (h >> (32 - pbits)) != prefix) continue;
+      atomicAdd(&hist[(h >> shift) & (uint32_t)(nbins - 1)], 1);
+    }
+    __syncthreads();
+    // block scan: thread t owns bins [per*t, per*t + per)
+    const int per = nbins / kSortThreads > 0 ? nbins / kSortThreads : 1;
+    int loc[4] = {0, 0, 0, 0};
+    int sum = 0;
+    if (tid * per < nbins) {
+      for (int q = 0; q < per; ++q) { loc[q] = hist[tid * per + q]; sum += loc[q]; }
+    }
+    int incl = sum;
+#pragma unroll
+    for (int s = 1; s < 32; s <<= 1) { int y = __shfl_up_sync(0xffffffffu, incl, s); if (lane >= s) incl += y; }
+    if (lane == 31) s_wsum[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int v = s_wsum[lane], x = v;
+#pragma unroll
+      for (int s = 1; s < 32; s <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, s); if (lane >= s) x += y; }
+      s_wsum[lane] = x - v;
+      if (lane == 31) s_total = x;
+    }
+    __syncthreads();
+    int c = below + s_wsum[warp] + incl - sum;   // eligible keys ordered before this thread's first bin
+    if (tid * per < nbins) {
+      for (int q = 0; q < per; ++q) {
+        const int cn = c + loc[q];
+        if (c < kBandMin && cn >= kBandMin) { s_found = 1; s_bin = tid * per + q; s_cum_in = cn; s_cum_ex = c; }
+        c = cn;
+      }
+    }
+    __syncthreads();
+    if (!s_found) {   // fewer than kBandMin keys left under this prefix (only possible at level 0): take all
+      if (tid == 0) { s_out[0] = (uint32_t)(below + s_total); s_out[1] = 0xffffffffu; }
+      __syncthreads();
+      return;
+    }
+    const uint32_t j = (uint32_t)s_bin;
+    if (s_cum_in <= kBandCap || level == 2) {
+      if (tid == 0) {
+        s_out[0] = (uint32_t)s_cum_in;
+        s_out[1] = (((prefix << nb) | j) << shift) | ((shift ? (1u << shift) : 1u) - 1u);
+      }
+      __syncthreads();
+      return;
+    }
+    below = s_cum_ex;
+    prefix = (prefix << nb) | j;
+    pbits += nb;
+  }
+}
+
 __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int b = blockIdx.x;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
   int n = P.count[b];
   if (n > P.cap) n = P.cap;
-  uint64_t* src = P.keys_a + (size_t)b * P.cap;
-  uint64_t* dst = P.keys_b + (size_t)b * P.cap;
-
-  // =============================== stable LSD radix sort (8-bit digits) ========================
-  {
-    int* whist = reinterpret_cast<int*>(smem_raw);            // [kSortWarps][256]
-    __shared__ unsigned long long s_and, s_or;
-    if (tid == 0) { s_and = ~0ull; s_or = 0ull; }
-    __syncthreads();
-    unsigned long long a = ~0ull, o = 0ull;
-    for (int i = tid; i < n; i += kSortThreads) { unsigned long long k = src[i]; a &= k; o |= k; }
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-      a &= __shfl_xor_sync(0xffffffffu, a, s);
-      o |= __shfl_xor_sync(0xffffffffu, o, s);
-    }
-    if (lane == 0) { atomicAnd(&s_and, a); atomicOr(&s_or, o); }
-    __syncthreads();
-    const unsigned long long varying = s_and ^ s_or;
-    // contiguous segment of the array owned by each warp (keeps the scatter stable)
-    const int per_warp = ((n + kSortWarps - 1) / kSortWarps + 31) / 32 * 32;
-    const int seg0 = min(n, warp * per_warp), seg1 = min(n, seg0 + per_warp);
-    for (int pass = 0; pass < 8 && n > 1; ++pass) {
-      const int sh = pass * 8;
-      if (((varying >> sh) & 0xffull) == 0) continue;  // digit identical for every key
-      for (int i = tid; i < kSortWarps * 256; i += kSortThreads) whist[i] = 0;
-      __syncthreads();
-      int* myh = whist + warp * 256;
-      for (int i = seg0 + lane; i - lane < seg1; i += 32) {
-        const bool valid = i < seg1;
-        const int d = valid ? (int)((src[i] >> sh) & 0xff) : 256 + lane;  // unique dummy digit per idle lane
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
-        if (valid && lane == __ffs(peers) - 1) myh[d] += __popc(peers);
-        __syncwarp();
-      }
-      __syncthreads();
-      // exclusive scan in (digit major, warp minor) order: thread t<256 owns digit t
-      __shared__ int digit_tot[256];
-      if (tid < 256) {
-        int s = 0;
-        for (int w = 0; w < kSortWarps; ++w) { int c = whist[w * 256 + tid]; whist[w * 256 + tid] = s; s += c; }
-        digit_tot[tid] = s;
-      }
-      __syncthreads();
-      if (warp == 0) {  // scan the 256 digit totals
-        int carry = 0;
-        for (int base = 0; base < 256; base += 32) {
-          int v = digit_tot[base + lane], x = v;
-#pragma unroll
-          for (int s = 1; s < 32; s <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, s); if (lane >= s) x += y; }
-          digit_tot[base + lane] = carry + x - v;
-          carry += __shfl_sync(0xffffffffu, x, 31);
-        }
-      }
-      __syncthreads();
-      if (tid < 256) {
-        const int base = digit_tot[tid];
-        for (int w = 0; w < kSortWarps; ++w) whist[w * 256 + tid] += base;
-      }
-      __syncthreads();
-      for (int i = seg0 + lane; i - lane < seg1; i += 32) {
-        const bool valid = i < seg1;
-        unsigned long long k = valid ? src[i] : 0ull;
-        const int d = valid ? (int)((k >> sh) & 0xff) : 256 + lane;
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
-        int pos = 0;
-        if (valid) pos = myh[d] + __popc(peers & ((1u << lane) - 1u));
-        __syncwarp();
-        if (valid && lane == __ffs(peers) - 1) myh[d] += __popc(peers);
-        __syncwarp();
-        if (valid) dst[pos] = k;
-      }
-      __syncthreads();
-      uint64_t* t = src; src = dst; dst = t;
-    }
-  }
-  __syncthreads();
+  uint64_t* gkeys = P.keys_a + (size_t)b * P.cap;
+  uint64_t* gtmp = P.keys_b + (size_t)b * P.cap;
+  const int m_total = min(n, P.max_nms);  // general.py:698-699
 
   // =============================== greedy NMS ================================================
-  const int m = min(n, P.max_nms);  // general.py:698-699
   float* kx1 = reinterpret_cast<float*>(smem_raw);
   float* ky1 = kx1 + P.max_det;
   float* kx2 = ky1 + P.max_det;
@@ -322,9 +407,61 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
   uint32_t* cmask = reinterpret_cast<uint32_t*>(ccls + kChunk);  // [kChunk][kChunkWords]
   unsigned char* calive = reinterpret_cast<unsigned char*>(cmask + kChunk * kChunkWords);
   __shared__ uint32_t s_alive[kChunkWords], s_new[kChunkWords];
-  __shared__ int s_K;
+  __shared__ int s_K, s_cnt;
+  __shared__ uint32_t s_sel[2];
+  const size_t nms_bytes = (size_t)((calive + kChunk) - smem_raw + 15) / 16 * 16;
+  uint64_t* band_a = reinterpret_cast<uint64_t*>(smem_raw + nms_bytes);
+  uint64_t* band_b = band_a + kBandCap;
+  int* scratch = reinterpret_cast<int*>(band_b + kBandCap);   // radix histograms [kSortWarps][256] / select [4096]
   if (tid == 0) s_K = 0;
   __syncthreads();
+
+  int consumed = 0;
+  uint32_t lo = 0;
+  bool have_lo = false;
+  while (consumed < m_total) {
+    if (s_K >= P.max_det) break;
+    // ---- next band of candidates, sorted
+    const uint64_t* src;
+    int band_n;
+    uint32_t T = 0xffffffffu;
+    if (!have_lo && n <= kBandCap) {
+      band_n = n;
+    } else {
+      select_band(gkeys, n, lo, have_lo, scratch, s_sel);
+      band_n = (int)s_sel[0];
+      T = s_sel[1];
+    }
+    if (band_n > kBandCap) {
+      // more equal scores than a band holds: sort everything once in global memory and walk the rest of it
+      // (the `consumed` smallest keys are exactly the bands already processed)
+      src = block_radix_sort(gkeys, gtmp, n, scratch) + consumed;
+      band_n = n - consumed;
+    } else {
+      __syncthreads();
+      if (tid == 0) s_cnt = 0;
+      __syncthreads();
+      for (int i0 = 0; i0 < n; i0 += kSortThreads) {
+        const int i = i0 + tid;
+        unsigned long long key = 0ull;
+        bool sel = false;
+        if (i < n) {
+          key = gkeys[i];
+          const uint32_t h = (uint32_t)(key >> 32);
+          sel = (!have_lo || h > lo) && h <= T;
+        }
+        const unsigned mk = __ballot_sync(0xffffffffu, sel);
+        int pos = 0;
+        if (lane == 0 && mk) pos = atomicAdd(&s_cnt, __popc(mk));
+        pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mk & ((1u << lane) - 1u));
+        if (sel) band_a[pos] = key;
+      }
+      __syncthreads();
+      src = block_radix_sort(band_a, band_b, band_n, scratch);
+      lo = T;
+      have_lo = true;
+    }
+    const int m = min(band_n, m_total - consumed);
 
   for (int base = 0; base < m; base += kChunk) {
     const int K = s_K;
@@ -424,6 +561,8 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
     }
     __syncthreads();
   }
+    consumed += band_n;
+  }
   if (tid == 0) P.counts_out[b] = s_K;
 }
 
@@ -513,9 +652,8 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
   if ((double)T > iou_thres) T = nextafterf(T, -INFINITY);
   N.thr_f = T; N.thr_nonneg = (T >= 0.0f) ? 1 : 0;
   N.out = out; N.counts_out = counts;
-  size_t sm_sort = (size_t)kSortWarps * 256 * 4;
   size_t sm_nms = (size_t)max_det * 5 * 4 + (size_t)kChunk * (5 + 4 + 2) * 4 + (size_t)kChunk * kChunkWords * 4 + kChunk;
-  size_t smem = sm_sort > sm_nms ? sm_sort : sm_nms;
+  size_t smem = (sm_nms + 15) / 16 * 16 + 2 * (size_t)kBandCap * 8 + (size_t)kSortWarps * 256 * 4;
   YB_CUDA(cudaFuncSetAttribute(k_sort_nms, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   k_sort_nms<<<B, kSortThreads, smem, s>>>(N);
   YB_LAUNCH_CHECK();
