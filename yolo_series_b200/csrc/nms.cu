@@ -181,6 +181,155 @@ __global__ void __launch_bounds__(256) k_filter(const FilterParams P) {
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// k_filter_best: best-class mode (multi_label == False, general.py:682-684), one THREAD per row.
+// The warps first stage a tile of rows into shared memory with coalesced loads (a row is `no` contiguous
+// values, rows are c_stride / no apart), then every thread walks its own row (row pitch odd -> no bank
+// conflicts).  In fused mode the class sigmoid is only evaluated where it can matter:
+//   conf_c = fl(sigmoid(l_c) * obj) and the reference takes the FIRST index of the maximum.  With M the largest
+//   class logit, every class with l_c < M - kLogitMargin has sigmoid(l_c) <= sigmoid(M - kLogitMargin) =: s_lo
+//   (sigmoid_rn_ is monotone up to a few ulps, covered by stepping s_lo up eight ulps), so if fl(s_lo' * obj) is
+//   strictly below conf(M) none of them can reach the maximum and only the classes within the margin are
+//   evaluated -- exactly.  When the test fails (saturated logits) every class is evaluated.
+// ------------------------------------------------------------------------------------------------
+constexpr int kFbThreads = 128;
+constexpr float kLogitMargin = 0.5f;
+
+template <bool FUSED, typename TL, int NV>
+__global__ void __launch_bounds__(kFbThreads) k_filter_best(const FilterParams P) {
+  extern __shared__ __align__(16) unsigned char fb_smem[];
+  float* tile = reinterpret_cast<float*>(fb_smem);             // [kFbThreads][pitch]
+  __shared__ uint64_t kbuf[kFbThreads];
+  __shared__ int s_n, s_base;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int pitch = P.no | 1;
+  const int b = blockIdx.x / P.blocks_per_img, blk = blockIdx.x - b * P.blocks_per_img;
+  const int row_begin = blk * P.rows_per_block;
+  const int row_end = min(P.A, row_begin + P.rows_per_block);
+  for (int t0 = row_begin; t0 < row_end; t0 += kFbThreads) {
+    const int t1 = min(row_end, t0 + kFbThreads);
+    if (tid == 0) s_n = 0;
+    // ---- stage rows [t0, t1): warp w owns rows t0 + w + 4k; four rows' loads are issued before their stores
+    constexpr int kWarpsFb = kFbThreads / 32;
+    for (int row0 = t0 + warp; row0 < t1; row0 += 4 * kWarpsFb) {
+      float v[4][NV];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int row = row0 + u * kWarpsFb;
+        const bool live = row < t1;
+        const float* src = nullptr;
+        const TL* lsrc = nullptr;
+        if (live) {
+          if (!FUSED) {
+            src = P.pred + ((size_t)b * P.A + row) * P.no;
+          } else {
+            int l = 0;
+            while (l + 1 < P.nl && row >= P.lv[l + 1].row_off) ++l;
+            const HeadLevelDev& L = P.lv[l];
+            const int cell = row - L.row_off;
+            const int a = L.magic_cells ? (int)__umulhi((unsigned)cell, L.magic_cells) : cell;
+            const int rem = cell - a * L.ny * L.nx;     // = gy * nx + gx
+            lsrc = reinterpret_cast<const TL*>(L.logits) + ((size_t)b * L.ny * L.nx + rem) * L.c_stride + a * P.no;
+          }
+        }
+#pragma unroll
+        for (int it = 0; it < NV; ++it) {
+          const int ch = it * 32 + lane;
+          v[u][it] = 0.f;
+          if (live && ch < P.no) v[u][it] = FUSED ? Elem<TL>::load(lsrc + ch) : __ldg(src + ch);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int row = row0 + u * kWarpsFb;
+        if (row < t1) {
+          float* dstp = tile + (row - t0) * pitch;
+#pragma unroll
+          for (int it = 0; it < NV; ++it) {
+            const int ch = it * 32 + lane;
+            if (ch < P.no) dstp[ch] = v[u][it];
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---- one thread per row
+    const int row = t0 + tid;
+    bool emit = false;
+    unsigned long long key = 0ull;
+    if (row < t1) {
+      const float* r = tile + tid * pitch;
+      float stride = 0.f, aw = 0.f, ah = 0.f;
+      int gx = 0, gy = 0;
+      if (FUSED) {
+        int l = 0;
+        while (l + 1 < P.nl && row >= P.lv[l + 1].row_off) ++l;
+        const HeadLevelDev& L = P.lv[l];
+        const int cell = row - L.row_off;
+        const int a = L.magic_cells ? (int)__umulhi((unsigned)cell, L.magic_cells) : cell;
+        const int rem = cell - a * L.ny * L.nx;
+        gy = L.magic_nx ? (int)__umulhi((unsigned)rem, L.magic_nx) : rem;
+        gx = rem - gy * L.nx;
+        stride = L.stride; aw = L.anchor_wh[2 * a]; ah = L.anchor_wh[2 * a + 1];
+      }
+      const float obj = FUSED ? sigmoid_rn_(r[4]) : r[4];
+      if (obj > P.conf_thres) {  // general.py:637,653
+        float best = -INFINITY;
+        int best_c = 0;
+        if (P.nc == 1) {          // general.py:670: conf = obj
+          best = obj;
+        } else if (!FUSED) {
+          for (int c = 0; c < P.nc; ++c) {
+            const float conf = __fmul_rn(r[5 + c], obj);
+            if (conf > best) { best = conf; best_c = c; }   // strict >: first index of the maximum
+          }
+        } else {
+          float M = -INFINITY;
+          for (int c = 0; c < P.nc; ++c) M = fmaxf(M, r[5 + c]);
+          const float conf_M = __fmul_rn(sigmoid_rn_(M), obj);
+          const float cut = M - kLogitMargin;
+          float s_lo = sigmoid_rn_(cut);
+          s_lo = __uint_as_float(__float_as_uint(s_lo) + 8u);            // eight ulps up (s_lo >= 0)
+          const bool margin_ok = __fmul_rn(s_lo, obj) < conf_M;          // NaN logits fail the test -> full scan
+          for (int c = 0; c < P.nc; ++c) {
+            const float lc = r[5 + c];
+            if (margin_ok && lc < cut) continue;
+            const float conf = __fmul_rn(sigmoid_rn_(lc), obj);
+            if (conf > best) { best = conf; best_c = c; }
+          }
+        }
+        if (best > P.conf_thres && class_allowed(P, best_c)) {  // general.py:684,688
+          emit = true;
+          key = ((unsigned long long)(~__float_as_uint(best)) << 32) | (uint32_t)row;
+          P.cls_of_row[(size_t)b * P.A + row] = (uint16_t)best_c;
+          if (FUSED) {
+            const float sx = sigmoid_rn_(r[0]), sy = sigmoid_rn_(r[1]), sw = sigmoid_rn_(r[2]), sh = sigmoid_rn_(r[3]);
+            const float bx = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(sx, 2.f), 0.5f), (float)gx), stride);
+            const float by = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(sy, 2.f), 0.5f), (float)gy), stride);
+            const float w2 = __fmul_rn(sw, 2.f), h2 = __fmul_rn(sh, 2.f);
+            *reinterpret_cast<float4*>(P.boxes + ((size_t)b * P.A + row) * 4) =
+                make_float4(bx, by, __fmul_rn(__fmul_rn(w2, w2), aw), __fmul_rn(__fmul_rn(h2, h2), ah));
+          }
+        }
+      }
+    }
+    const unsigned mk = __ballot_sync(0xffffffffu, emit);
+    int pos = 0;
+    if (lane == 0 && mk) pos = atomicAdd(&s_n, __popc(mk));
+    pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mk & ((1u << lane) - 1u));
+    if (emit) kbuf[pos] = key;
+    __syncthreads();
+    if (tid == 0) s_base = s_n ? atomicAdd(P.count + b, s_n) : 0;
+    __syncthreads();
+    if (tid < s_n) {
+      const int slot = s_base + tid;
+      if (slot < P.cap) P.keys[(size_t)b * P.cap + slot] = kbuf[tid];
+      else if (P.overflow) *P.overflow = 1;
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace yb
 
 namespace yb {
@@ -627,19 +776,49 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
     F.rows_per_block = (A + bpi - 1) / bpi;
     F.blocks_per_img = (A + F.rows_per_block - 1) / F.rows_per_block;
     const int grid = B * F.blocks_per_img;
-    const int nv = (F.no + 31) / 32;
+    const size_t fb_smem = (size_t)kFbThreads * (F.no | 1) * 4;
+    if (!F.multi_label && fb_smem <= 160 * 1024) {
+      // best-class mode: one thread per row over a staged tile
+      int bpi2 = (num_sms() * 8 + B - 1) / B;
+      if (bpi2 > (A + kFbThreads - 1) / kFbThreads) bpi2 = (A + kFbThreads - 1) / kFbThreads;
+      if (bpi2 < 1) bpi2 = 1;
+      F.rows_per_block = ((A + bpi2 - 1) / bpi2 + kFbThreads - 1) / kFbThreads * kFbThreads;
+      F.blocks_per_img = (A + F.rows_per_block - 1) / F.rows_per_block;
+      const int grid2 = B * F.blocks_per_img;
+      const int nvb = (F.no + 31) / 32;
+#define YB_FB_LAUNCH_T(FU, T, NVV)                                                                                     \
+      do {                                                                                                             \
+        YB_CUDA(cudaFuncSetAttribute(k_filter_best<FU, T, NVV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_smem)); \
+        k_filter_best<FU, T, NVV><<<grid2, kFbThreads, fb_smem, s>>>(F);                                               \
+      } while (0)
+#define YB_FB_LAUNCH(NVV)                                                     \
+      do {                                                                    \
+        if (!fused) YB_FB_LAUNCH_T(false, float, NVV);                        \
+        else if (logits_dtype == YB_F32) YB_FB_LAUNCH_T(true, float, NVV);    \
+        else YB_FB_LAUNCH_T(true, __nv_bfloat16, NVV);                        \
+      } while (0)
+      if (nvb <= 1) YB_FB_LAUNCH(1);
+      else if (nvb == 2) YB_FB_LAUNCH(2);
+      else if (nvb == 3) YB_FB_LAUNCH(3);
+      else if (nvb == 4) YB_FB_LAUNCH(4);
+      else YB_FB_LAUNCH(8);
+#undef YB_FB_LAUNCH
+#undef YB_FB_LAUNCH_T
+    } else {
+      const int nv = (F.no + 31) / 32;
 #define YB_FILTER_LAUNCH(NVV)                                                              \
-    do {                                                                                   \
-      if (!fused) k_filter<false, float, NVV><<<grid, 256, 0, s>>>(F);                     \
-      else if (logits_dtype == YB_F32) k_filter<true, float, NVV><<<grid, 256, 0, s>>>(F); \
-      else k_filter<true, __nv_bfloat16, NVV><<<grid, 256, 0, s>>>(F);                     \
-    } while (0)
-    if (nv <= 1) YB_FILTER_LAUNCH(1);
-    else if (nv == 2) YB_FILTER_LAUNCH(2);
-    else if (nv == 3) YB_FILTER_LAUNCH(3);
-    else if (nv == 4) YB_FILTER_LAUNCH(4);
-    else YB_FILTER_LAUNCH(8);
+      do {                                                                                   \
+        if (!fused) k_filter<false, float, NVV><<<grid, 256, 0, s>>>(F);                     \
+        else if (logits_dtype == YB_F32) k_filter<true, float, NVV><<<grid, 256, 0, s>>>(F); \
+        else k_filter<true, __nv_bfloat16, NVV><<<grid, 256, 0, s>>>(F);                     \
+      } while (0)
+      if (nv <= 1) YB_FILTER_LAUNCH(1);
+      else if (nv == 2) YB_FILTER_LAUNCH(2);
+      else if (nv == 3) YB_FILTER_LAUNCH(3);
+      else if (nv == 4) YB_FILTER_LAUNCH(4);
+      else YB_FILTER_LAUNCH(8);
 #undef YB_FILTER_LAUNCH
+    }
     YB_LAUNCH_CHECK();
   }
   NmsParams N;
