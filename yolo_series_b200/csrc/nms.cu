@@ -25,6 +25,7 @@ struct HeadLevelDev {  // fused decode source (yb_decode_nms)
   float anchor_wh[2 * YB_MAX_ANCHORS];
   int row_off;
   unsigned magic_cells, magic_nx;   // floor(2^32 / d) + 1 for d = ny*nx and d = nx
+  int blk_off;                      // k_filter_cells: first block (within an image) of this level
 };
 
 struct FilterParams {
@@ -39,6 +40,7 @@ struct FilterParams {
   uint32_t class_mask[kMaxClassWords];
   int cap;
   int rows_per_block, blocks_per_img;   // launch geometry: grid = B * blocks_per_img
+  int cells_per_block;                  // k_filter_cells
   // outputs
   int* count;            // [B]
   uint64_t* keys;        // [B][cap]
@@ -190,10 +192,63 @@ __global__ void __launch_bounds__(256) k_filter(const FilterParams P) {
 //   class logit, every class with l_c < M - kLogitMargin has sigmoid(l_c) <= sigmoid(M - kLogitMargin) =: s_lo
 //   (sigmoid_rn_ is monotone up to a few ulps, covered by stepping s_lo up eight ulps), so if fl(s_lo' * obj) is
 //   strictly below conf(M) none of them can reach the maximum and only the classes within the margin are
-//   evaluated -- exactly.  When the test fails (saturated logits) every class is evaluated.
+//   evaluated -- exactly (classes equal to M reuse conf(M)).  When the test fails (saturated logits) every
+//   class is evaluated.
 // ------------------------------------------------------------------------------------------------
 constexpr int kFbThreads = 128;
-constexpr float kLogitMargin = 0.5f;
+constexpr int kFbInflight = 8;       // rows whose loads a warp has in flight while staging
+constexpr float kLogitMargin = 0.015625f;
+
+// One row of the best-class filter: r = the row's `no` values (logits when FUSED, decoded predictions otherwise).
+// Returns true and the sort key when the row is a candidate; writes its class (and decoded box when FUSED).
+template <bool FUSED>
+__device__ __forceinline__ bool fb_process_row(const FilterParams& P, const float* r, int b, int row, int gx, int gy,
+                                               float stride, float aw, float ah, unsigned long long& key) {
+  bool emit = false;
+  const float obj = FUSED ? sigmoid_rn_(r[4]) : r[4];
+  if (obj > P.conf_thres) {  // general.py:637,653
+    float best = -INFINITY;
+    int best_c = 0;
+    if (P.nc == 1) {          // general.py:670: conf = obj
+      best = obj;
+    } else if (!FUSED) {
+      for (int c = 0; c < P.nc; ++c) {
+        const float conf = __fmul_rn(r[5 + c], obj);
+        if (conf > best) { best = conf; best_c = c; }   // strict >: first index of the maximum
+      }
+    } else {
+      float M = -INFINITY;
+#pragma unroll 8
+      for (int c = 0; c < P.nc; ++c) M = fmaxf(M, r[5 + c]);
+      const float conf_M = __fmul_rn(sigmoid_rn_(M), obj);
+      const float cut = M - kLogitMargin;
+      float s_lo = sigmoid_rn_(cut);
+      s_lo = __uint_as_float(__float_as_uint(s_lo) + 8u);            // eight ulps up (s_lo >= 0)
+      const bool margin_ok = __fmul_rn(s_lo, obj) < conf_M;          // NaN logits fail the test -> full scan
+#pragma unroll 8
+      for (int c = 0; c < P.nc; ++c) {
+        const float lc = r[5 + c];
+        if (margin_ok && lc < cut) continue;
+        const float conf = lc == M ? conf_M : __fmul_rn(sigmoid_rn_(lc), obj);   // same logit, same product
+        if (conf > best) { best = conf; best_c = c; }
+      }
+    }
+    if (best > P.conf_thres && class_allowed(P, best_c)) {  // general.py:684,688
+      emit = true;
+      key = ((unsigned long long)(~__float_as_uint(best)) << 32) | (uint32_t)row;
+      P.cls_of_row[(size_t)b * P.A + row] = (uint16_t)best_c;
+      if (FUSED) {
+        const float sx = sigmoid_rn_(r[0]), sy = sigmoid_rn_(r[1]), sw = sigmoid_rn_(r[2]), sh = sigmoid_rn_(r[3]);
+        const float bx = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(sx, 2.f), 0.5f), (float)gx), stride);
+        const float by = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(sy, 2.f), 0.5f), (float)gy), stride);
+        const float w2 = __fmul_rn(sw, 2.f), h2 = __fmul_rn(sh, 2.f);
+        *reinterpret_cast<float4*>(P.boxes + ((size_t)b * P.A + row) * 4) =
+            make_float4(bx, by, __fmul_rn(__fmul_rn(w2, w2), aw), __fmul_rn(__fmul_rn(h2, h2), ah));
+      }
+    }
+  }
+  return emit;
+}
 
 template <bool FUSED, typename TL, int NV>
 __global__ void __launch_bounds__(kFbThreads) k_filter_best(const FilterParams P) {
@@ -209,12 +264,12 @@ __global__ void __launch_bounds__(kFbThreads) k_filter_best(const FilterParams P
   for (int t0 = row_begin; t0 < row_end; t0 += kFbThreads) {
     const int t1 = min(row_end, t0 + kFbThreads);
     if (tid == 0) s_n = 0;
-    // ---- stage rows [t0, t1): warp w owns rows t0 + w + 4k; four rows' loads are issued before their stores
+    // ---- stage rows [t0, t1): warp w owns rows t0 + w + 4k; eight rows' loads are issued before their stores
     constexpr int kWarpsFb = kFbThreads / 32;
-    for (int row0 = t0 + warp; row0 < t1; row0 += 4 * kWarpsFb) {
-      float v[4][NV];
+    for (int row0 = t0 + warp; row0 < t1; row0 += kFbInflight * kWarpsFb) {
+      float v[kFbInflight][NV];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kFbInflight; ++u) {
         const int row = row0 + u * kWarpsFb;
         const bool live = row < t1;
         const float* src = nullptr;
@@ -240,7 +295,7 @@ __global__ void __launch_bounds__(kFbThreads) k_filter_best(const FilterParams P
         }
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < kFbInflight; ++u) {
         const int row = row0 + u * kWarpsFb;
         if (row < t1) {
           float* dstp = tile + (row - t0) * pitch;
@@ -272,46 +327,98 @@ __global__ void __launch_bounds__(kFbThreads) k_filter_best(const FilterParams P
         gx = rem - gy * L.nx;
         stride = L.stride; aw = L.anchor_wh[2 * a]; ah = L.anchor_wh[2 * a + 1];
       }
-      const float obj = FUSED ? sigmoid_rn_(r[4]) : r[4];
-      if (obj > P.conf_thres) {  // general.py:637,653
-        float best = -INFINITY;
-        int best_c = 0;
-        if (P.nc == 1) {          // general.py:670: conf = obj
-          best = obj;
-        } else if (!FUSED) {
-          for (int c = 0; c < P.nc; ++c) {
-            const float conf = __fmul_rn(r[5 + c], obj);
-            if (conf > best) { best = conf; best_c = c; }   // strict >: first index of the maximum
-          }
-        } else {
-          float M = -INFINITY;
-          for (int c = 0; c < P.nc; ++c) M = fmaxf(M, r[5 + c]);
-          const float conf_M = __fmul_rn(sigmoid_rn_(M), obj);
-          const float cut = M - kLogitMargin;
-          float s_lo = sigmoid_rn_(cut);
-          s_lo = __uint_as_float(__float_as_uint(s_lo) + 8u);            // eight ulps up (s_lo >= 0)
-          const bool margin_ok = __fmul_rn(s_lo, obj) < conf_M;          // NaN logits fail the test -> full scan
-          for (int c = 0; c < P.nc; ++c) {
-            const float lc = r[5 + c];
-            if (margin_ok && lc < cut) continue;
-            const float conf = __fmul_rn(sigmoid_rn_(lc), obj);
-            if (conf > best) { best = conf; best_c = c; }
-          }
-        }
-        if (best > P.conf_thres && class_allowed(P, best_c)) {  // general.py:684,688
-          emit = true;
-          key = ((unsigned long long)(~__float_as_uint(best)) << 32) | (uint32_t)row;
-          P.cls_of_row[(size_t)b * P.A + row] = (uint16_t)best_c;
-          if (FUSED) {
-            const float sx = sigmoid_rn_(r[0]), sy = sigmoid_rn_(r[1]), sw = sigmoid_rn_(r[2]), sh = sigmoid_rn_(r[3]);
-            const float bx = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(sx, 2.f), 0.5f), (float)gx), stride);
-            const float by = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(sy, 2.f), 0.5f), (float)gy), stride);
-            const float w2 = __fmul_rn(sw, 2.f), h2 = __fmul_rn(sh, 2.f);
-            *reinterpret_cast<float4*>(P.boxes + ((size_t)b * P.A + row) * 4) =
-                make_float4(bx, by, __fmul_rn(__fmul_rn(w2, w2), aw), __fmul_rn(__fmul_rn(h2, h2), ah));
-          }
+      emit = fb_process_row<FUSED>(P, r, b, row, gx, gy, stride, aw, ah, key);
+    }
+    const unsigned mk = __ballot_sync(0xffffffffu, emit);
+    int pos = 0;
+    if (lane == 0 && mk) pos = atomicAdd(&s_n, __popc(mk));
+    pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mk & ((1u << lane) - 1u));
+    if (emit) kbuf[pos] = key;
+    __syncthreads();
+    if (tid == 0) s_base = s_n ? atomicAdd(P.count + b, s_n) : 0;
+    __syncthreads();
+    if (tid < s_n) {
+      const int slot = s_base + tid;
+      if (slot < P.cap) P.keys[(size_t)b * P.cap + slot] = kbuf[tid];
+      else if (P.overflow) *P.overflow = 1;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_filter_cells: fused best-class filter reading the head maps cell-major.  A head level stores, per grid cell,
+// the na*no logits of all its anchors contiguously (c_stride values per cell), so a tile of consecutive cells is
+// ONE contiguous span: it is staged with 16-byte coalesced loads (cell pitch c_stride + 1 in shared memory keeps
+// the thread-per-row walk conflict-free) and thread (a, cell) handles prediction row row_off + a*ny*nx + cell.
+// Block -> (image, level, cell range) through lv[].blk_off.
+// ------------------------------------------------------------------------------------------------
+template <typename TL> struct Vec4Load;
+template <> struct Vec4Load<float> {
+  static __device__ __forceinline__ float4 load(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+};
+template <> struct Vec4Load<__nv_bfloat16> {
+  static __device__ __forceinline__ float4 load(const __nv_bfloat16* p) {
+    const uint2 u = __ldg(reinterpret_cast<const uint2*>(p));
+    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&u.x), c = *reinterpret_cast<const __nv_bfloat162*>(&u.y);
+    return make_float4(__low2float(a), __high2float(a), __low2float(c), __high2float(c));
+  }
+};
+
+template <typename TL>
+__global__ void __launch_bounds__(kFbThreads) k_filter_cells(const FilterParams P) {
+  extern __shared__ __align__(16) unsigned char fb_smem[];
+  float* tile = reinterpret_cast<float*>(fb_smem);             // [cells_per_tile][c_stride + 1]
+  __shared__ uint64_t kbuf[kFbThreads];
+  __shared__ int s_n, s_base;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int b = blockIdx.x / P.blocks_per_img;
+  int blk = blockIdx.x - b * P.blocks_per_img;
+  int l = 0;
+  while (l + 1 < P.nl && blk >= P.lv[l + 1].blk_off) ++l;
+  blk -= P.lv[l].blk_off;
+  const HeadLevelDev& L = P.lv[l];
+  const int ncells = L.ny * L.nx;
+  const int cpt = kFbThreads / P.na;                           // cells per tile (thread = (anchor, cell))
+  const int cell_begin = blk * P.cells_per_block;
+  const int cell_end = min(ncells, cell_begin + P.cells_per_block);
+  const int pitch = L.c_stride + 1;
+  const TL* lbase = reinterpret_cast<const TL*>(L.logits) + (size_t)b * ncells * L.c_stride;
+  const int a = tid / cpt, cl = tid - a * cpt;
+  for (int c0 = cell_begin; c0 < cell_end; c0 += cpt) {
+    const int nc_tile = min(cpt, cell_end - c0);
+    if (tid == 0) s_n = 0;
+    // ---- stage nc_tile * c_stride contiguous values
+    const TL* src = lbase + (size_t)c0 * L.c_stride;
+    const int nvec = nc_tile * L.c_stride / 4;
+    for (int i0 = 0; i0 < nvec; i0 += 8 * kFbThreads) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * kFbThreads + tid;
+        if (i < nvec) v[u] = Vec4Load<TL>::load(src + 4 * (size_t)i);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u * kFbThreads + tid;
+        if (i < nvec) {
+          const int e = 4 * i;
+          const int cell = e / L.c_stride, off = e - cell * L.c_stride;   // c_stride % 4 == 0: one cell per vector
+          float* d = tile + cell * pitch + off;
+          d[0] = v[u].x; d[1] = v[u].y; d[2] = v[u].z; d[3] = v[u].w;
         }
       }
+    }
+    __syncthreads();
+    bool emit = false;
+    unsigned long long key = 0ull;
+    if (a < P.na && cl < nc_tile) {
+      const int cell = c0 + cl;
+      const int gy = L.magic_nx ? (int)__umulhi((unsigned)cell, L.magic_nx) : cell;
+      const int gx = cell - gy * L.nx;
+      const int row = L.row_off + a * ncells + cell;
+      emit = fb_process_row<true>(P, tile + cl * pitch + a * P.no, b, row, gx, gy, L.stride, L.anchor_wh[2 * a],
+                                  L.anchor_wh[2 * a + 1], key);
     }
     const unsigned mk = __ballot_sync(0xffffffffu, emit);
     int pos = 0;
@@ -777,7 +884,40 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
     F.blocks_per_img = (A + F.rows_per_block - 1) / F.rows_per_block;
     const int grid = B * F.blocks_per_img;
     const size_t fb_smem = (size_t)kFbThreads * (F.no | 1) * 4;
-    if (!F.multi_label && fb_smem <= 160 * 1024) {
+    bool cells_ok = fused && !F.multi_label && F.na >= 1 && F.na <= 8;
+    int max_cs = 0;
+    for (int l = 0; cells_ok && l < F.nl; ++l) {
+      const HeadLevelDev& L = F.lv[l];
+      const size_t es = L.dtype == YB_F32 ? 4 : 2;
+      cells_ok = L.c_stride % 4 == 0 && L.c_stride >= F.na * F.no && (uintptr_t)L.logits % 16 == 0 &&
+                 ((size_t)L.c_stride * es) % 16 == 0;
+      if (L.c_stride > max_cs) max_cs = L.c_stride;
+    }
+    const int cpt = cells_ok ? kFbThreads / F.na : 0;
+    const size_t cells_smem = cells_ok ? (size_t)cpt * (max_cs + 1) * 4 : 0;
+    if (cells_ok && cells_smem <= 100 * 1024) {
+      // cells per block: ~8 resident blocks per SM over the batch, whole tiles
+      long long total_cells = 0;
+      for (int l = 0; l < F.nl; ++l) total_cells += (long long)F.lv[l].ny * F.lv[l].nx;
+      long long want = (total_cells * B + (long long)num_sms() * 8 - 1) / ((long long)num_sms() * 8);
+      int cpb = (int)((want + cpt - 1) / cpt) * cpt;
+      if (cpb < cpt) cpb = cpt;
+      F.cells_per_block = cpb;
+      int off = 0;
+      for (int l = 0; l < F.nl; ++l) {
+        F.lv[l].blk_off = off;
+        off += (F.lv[l].ny * F.lv[l].nx + cpb - 1) / cpb;
+      }
+      F.blocks_per_img = off;
+      const int grid3 = B * off;
+      if (logits_dtype == YB_F32) {
+        YB_CUDA(cudaFuncSetAttribute(k_filter_cells<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cells_smem));
+        k_filter_cells<float><<<grid3, kFbThreads, cells_smem, s>>>(F);
+      } else {
+        YB_CUDA(cudaFuncSetAttribute(k_filter_cells<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cells_smem));
+        k_filter_cells<__nv_bfloat16><<<grid3, kFbThreads, cells_smem, s>>>(F);
+      }
+    } else if (!F.multi_label && fb_smem <= 160 * 1024) {
       // best-class mode: one thread per row over a staged tile
       int bpi2 = (num_sms() * 8 + B - 1) / B;
       if (bpi2 > (A + kFbThreads - 1) / kFbThreads) bpi2 = (A + kFbThreads - 1) / kFbThreads;
