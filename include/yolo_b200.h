@@ -81,6 +81,13 @@ typedef struct {
 
 int yb_conv2d(const yb_conv_desc* d, void* stream);
 
+/* Reusable plan for one bf16 convolution: the TMA descriptors and tile geometry that yb_conv2d derives on
+ * every call are built once (what the engine does per op).  Tensors named by the descriptor must stay valid. */
+typedef struct yb_conv_plan yb_conv_plan;
+int yb_conv_plan_create(const yb_conv_desc* d, yb_conv_plan** out);
+int yb_conv_plan_launch(const yb_conv_plan* p, void* stream);
+void yb_conv_plan_destroy(yb_conv_plan* p);
+
 /* ------------------------------------------------------------------ pooling / data movement */
 /* MP: MaxPool2d(2,2) (models/common.py:30-36) */
 int yb_maxpool2x2(const yb_tensor* x, const yb_tensor* y, void* stream);

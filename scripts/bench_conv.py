@@ -30,15 +30,18 @@ for spec in sys.argv[1:]:
     d.weight, d.bias = wp.data_ptr(), bp.data_ptr()
     d.cin_pad, d.cout_pad, d.k, d.stride, d.act, d.upsample = cx, co, k, s, 1, 1
     d.tile_n, d.stages = tile_n, stages
+    plan = C.c_void_p()
+    _lib.check(L.yb_conv_plan_create(C.byref(d), C.byref(plan)))
     for _ in range(3):
-        _lib.check(L.yb_conv2d(C.byref(d), _lib.stream_ptr()))
+        _lib.check(L.yb_conv_plan_launch(plan, _lib.stream_ptr()))
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(REPS):
-        _lib.check(L.yb_conv2d(C.byref(d), _lib.stream_ptr()))
+        _lib.check(L.yb_conv_plan_launch(plan, _lib.stream_ptr()))
     e1.record()
     torch.cuda.synchronize()
+    L.yb_conv_plan_destroy(plan)
     ms = e0.elapsed_time(e1) / REPS
     fl = 2 * ci * co * k * k * ho * ho * B
     by = B * (h * h * cx + ho * ho * co) * 2

@@ -16,7 +16,8 @@ OP_CONV, OP_MAXPOOL2, OP_POOL_S1, OP_SPP3, OP_UPSAMPLE2, OP_COPY, OP_ADD, OP_STE
 MAX_LEVELS, MAX_ANCHORS = 8, 8
 
 EXPORTS = [
-    'yb_last_error', 'yb_abi_version', 'yb_conv2d', 'yb_maxpool2x2', 'yb_maxpool_s1', 'yb_spp3',
+    'yb_last_error', 'yb_abi_version', 'yb_conv2d', 'yb_conv_plan_create', 'yb_conv_plan_launch',
+    'yb_conv_plan_destroy', 'yb_maxpool2x2', 'yb_maxpool_s1', 'yb_spp3',
     'yb_upsample2x', 'yb_copy', 'yb_add', 'yb_stage_input', 'yb_stem_conv', 'yb_decode', 'yb_nms_workspace_bytes',
     'yb_nms', 'yb_decode_nms', 'yb_engine_create', 'yb_engine_forward', 'yb_engine_num_launches', 'yb_engine_profile',
     'yb_engine_destroy',
@@ -67,6 +68,10 @@ def lib():
     L.yb_engine_num_launches.argtypes = [C.c_void_p]
     L.yb_engine_profile.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.c_void_p]
     L.yb_conv2d.argtypes = [C.POINTER(ConvDesc), C.c_void_p]
+    L.yb_conv_plan_create.argtypes = [C.POINTER(ConvDesc), C.POINTER(C.c_void_p)]
+    L.yb_conv_plan_launch.argtypes = [C.c_void_p, C.c_void_p]
+    L.yb_conv_plan_destroy.argtypes = [C.c_void_p]
+    L.yb_conv_plan_destroy.restype = None
     for name in ('yb_maxpool2x2', 'yb_upsample2x', 'yb_copy'):
         getattr(L, name).argtypes = [C.POINTER(Tensor), C.POINTER(Tensor), C.c_void_p]
     L.yb_maxpool_s1.argtypes = [C.POINTER(Tensor), C.POINTER(Tensor), C.c_int, C.c_void_p]

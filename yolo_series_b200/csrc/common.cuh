@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/yolo_b200.h"
@@ -68,6 +69,24 @@ template <> struct Elem<__nv_bfloat16> {
   static __device__ __forceinline__ float load(const __nv_bfloat16* p) { return __bfloat162float(*p); }
   static __device__ __forceinline__ void store(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
 };
+
+// Launch with the programmatic-stream-serialization attribute (the kernel must call griddepcontrol.wait before
+// touching anything an earlier kernel writes).  Captured into CUDA graphs as a programmatic dependency edge.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid, 1, 1);
+  cfg.blockDim = dim3((unsigned)block, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  static const bool off = getenv("YB_NO_PDL") != nullptr;   // debugging aid: plain stream-ordered launches
+  cfg.attrs = at;
+  cfg.numAttrs = off ? 0 : 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 // internal launchers shared by the C ABI wrappers and the engine
 int conv_fp32_launch(const yb_conv_desc& d, cudaStream_t s);

@@ -86,6 +86,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();   // set-up done: the next kernel's CTAs may take SMs as ours retire
+  pdl_wait();                // activations written by the previous kernel are visible from here on
   const int tiles_m_per_img = G.tiles_w * G.tiles_h;
   const int stages_per_tile = 3 * G.kchunks;
 
@@ -310,8 +312,7 @@ int conv3_tc_launch(const Conv3Plan* P, cudaStream_t s) {
     YB_CUDA(cudaFuncSetAttribute(k_conv3_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  k_conv3_tc<<<P->grid, kTcThreads, P->smem, s>>>(P->args);
-  YB_LAUNCH_CHECK();
+  YB_CUDA(launch_pdl(k_conv3_tc, P->grid, kTcThreads, P->smem, s, P->args));
   return YB_OK;
 }
 

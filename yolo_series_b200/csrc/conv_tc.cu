@@ -24,7 +24,8 @@ struct ConvTcArgs {
   const float* bias;
   int tiles_n, tiles_w, tiles_h;   // tile grid; m tiles = tiles_w * tiles_h * images
   int BW, BH, BN, BK;              // spatial box, N tile, K chunk (channels)
-  int taps, ksz, stride, pad;
+  int taps, kw, stride_h, stride_w, pad_h, pad_w;   // taps = kh * kw, tap = dy * kw + dx
+  int resident;                    // 1: all weight tiles of the CTA's N tile stay in shared memory
   int kchunks;                     // ceil(Cin / BK)
   int stages;
   int act; float slope;
@@ -50,17 +51,21 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   unsigned char* tiles_ptr = smem_dyn + (tiles - raw);
   const uint32_t a_bytes = 128u * G.BK * 2u;
   const uint32_t b_bytes = (uint32_t)G.BN * G.BK * 2u;
-  const uint32_t stage_bytes = a_bytes + b_bytes;
+  // resident mode: [all taps x chunks weight tiles][A ring]; streaming mode: ring of (A, B) stages
+  const uint32_t res_bytes = G.resident ? b_bytes * (uint32_t)(G.taps * G.kchunks) : 0u;
+  const uint32_t stage_bytes = G.resident ? a_bytes : a_bytes + b_bytes;
+  const uint32_t ring = tiles + res_bytes;
   const uint32_t out_es = G.out_f32 ? 4u : 2u;
-  const uint32_t pipe_bytes = stage_bytes * G.stages;
-  const uint32_t staging = tiles + pipe_bytes;                       // 1024-aligned (stage_bytes % 1024 == 0)
+  const uint32_t pipe_bytes = res_bytes + stage_bytes * G.stages;
+  const uint32_t staging = tiles + pipe_bytes;                       // 1024-aligned (all pieces are multiples of 1024)
   const uint32_t staging_bytes = ((uint32_t)G.BN * out_es + 127u) / 128u * 16384u;   // 128 rows x 128 B per group
   unsigned char* aux = tiles_ptr + pipe_bytes + staging_bytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(aux);  // full[S], empty[S], tmem_full[2], tmem_empty[2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux + 8 * (2 * G.stages + 4));
-  float* bias_s = reinterpret_cast<float*>(aux + 8 * (2 * G.stages + 4) + 16);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(aux);  // full[S], empty[S], tmem_full[2], tmem_empty[2], resident
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux + 8 * (2 * G.stages + 6));
+  float* bias_s = reinterpret_cast<float*>(aux + 8 * (2 * G.stages + 6) + 16);
   const uint32_t bar_full0 = smem_u32(bars), bar_empty0 = bar_full0 + 8u * G.stages;
   const uint32_t bar_tfull0 = bar_full0 + 16u * G.stages, bar_tempty0 = bar_tfull0 + 16u;
+  const uint32_t bar_res = bar_tempty0 + 16u;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&G.tm_a);
@@ -68,6 +73,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     for (int i = 0; i < G.n_store_maps; ++i) tma_prefetch_desc(&G.tm_y[i]);
     for (int s = 0; s < G.stages; ++s) { mbar_init(bar_full0 + 8u * s, 1); mbar_init(bar_empty0 + 8u * s, 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull0 + 8u * i, 1); mbar_init(bar_tempty0 + 8u * i, 1); }
+    mbar_init(bar_res, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
@@ -82,36 +88,54 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   const uint32_t tmem_base = *tmem_slot;
   const int total_chunks = G.taps * G.kchunks;
   const int tiles_m_per_img = G.tiles_w * G.tiles_h;
+  // Tile walk.  Streaming: t = blockIdx.x + i * grid over (m, n) pairs, n fastest.  Resident: the CTA keeps one
+  // N tile (blockIdx.x % tiles_n) and strides over the M tiles.
+  const int res_n = blockIdx.x % G.tiles_n;
+  const int t_first = G.resident ? blockIdx.x / G.tiles_n : blockIdx.x;
+  const int t_step = G.resident ? gridDim.x / G.tiles_n : gridDim.x;
+  const int t_end = G.resident ? G.total_tiles / G.tiles_n : G.total_tiles;
+  if (G.resident && warp == 0) {
+    // weights are constants: fetch them while the previous kernel is still draining
+    if (elect_one()) {
+      mbar_expect_tx(bar_res, res_bytes);
+      for (int tap = 0; tap < G.taps; ++tap)
+        for (int kk = 0; kk < G.kchunks; ++kk)
+          tma_load_3d(&G.tm_b, bar_res, tiles + (uint32_t)(tap * G.kchunks + kk) * b_bytes, kk * G.BK, tap, res_n * G.BN);
+    }
+    __syncwarp();
+  }
+  pdl_launch_dependents();   // set-up done: the next kernel's CTAs may take SMs as ours retire
+  pdl_wait();                // activations written by the previous kernel are visible from here on
 
   if (warp == 0) {
     // ================================ TMA producer ================================
     // Warp-uniform control flow, one elected lane issues the copies (coordinates live in uniform registers).
-    const uint32_t tx = (uint32_t)(G.BW * G.BH) * G.BK * 2u + b_bytes;
+    const uint32_t tx = (uint32_t)(G.BW * G.BH) * G.BK * 2u + (G.resident ? 0u : b_bytes);
     uint32_t s = 0, ph = 1;  // ring slot + parity to wait for on its empty barrier
-    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x) {
-      const int n_tile = t % G.tiles_n;
-      int m_tile = t / G.tiles_n;
+    for (int t = t_first; t < t_end; t += t_step) {
+      const int n_tile = G.resident ? res_n : t % G.tiles_n;
+      int m_tile = G.resident ? t : t / G.tiles_n;
       const int img = m_tile / tiles_m_per_img;
       m_tile -= img * tiles_m_per_img;
       const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
       const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
       int dy = 0, dx = 0;
       for (int tap = 0; tap < G.taps; ++tap) {
-        const int cw = w0 * G.stride + dx - G.pad;
-        const int chh = G.flat ? 0 : h0 * G.stride + dy - G.pad;
+        const int cw = w0 * G.stride_w + dx - G.pad_w;
+        const int chh = G.flat ? 0 : h0 * G.stride_h + dy - G.pad_h;
         for (int kk = 0; kk < G.kchunks; ++kk) {
           mbar_wait(bar_empty0 + 8u * s, ph);
           if (elect_one()) {
             const uint32_t full = bar_full0 + 8u * s;
             mbar_expect_tx(full, tx);
-            const uint32_t sa = tiles + s * stage_bytes;
+            const uint32_t sa = ring + s * stage_bytes;
             tma_load_4d(&G.tm_a, full, sa, kk * G.BK, cw, chh, img);
-            tma_load_3d(&G.tm_b, full, sa + a_bytes, kk * G.BK, tap, n0);
+            if (!G.resident) tma_load_3d(&G.tm_b, full, sa + a_bytes, kk * G.BK, tap, n0);
           }
           __syncwarp();
           if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
         }
-        if (++dx == G.ksz) { dx = 0; ++dy; }
+        if (++dx == G.kw) { dx = 0; ++dy; }
       }
     }
   } else if (warp == 1) {
@@ -121,9 +145,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     const int nk = G.BK / 16;
     const uint32_t hi32 = (uint32_t)(make_smem_desc(0, sbo, (uint32_t)G.sw_mode) >> 32);
     const uint32_t boff = a_bytes >> 4;
+    const uint32_t bres = (tiles >> 4) & 0x3FFF, bstep = b_bytes >> 4;
+    if (G.resident) mbar_wait(bar_res, 0);
     uint32_t s = 0, ph = 0;
     int it = 0;
-    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
+    for (int t = t_first; t < t_end; t += t_step, ++it) {
       const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
       mbar_wait(bar_tempty0 + 8u * acc, aph ^ 1u);       // epilogue has drained this accumulator
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -131,17 +157,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
       for (int c = 0; c < total_chunks; ++c) {
         mbar_wait(bar_full0 + 8u * s, ph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t da = ((tiles + s * stage_bytes) >> 4) & 0x3FFF;
+        const uint32_t da = ((ring + s * stage_bytes) >> 4) & 0x3FFF;
+        const uint32_t db = G.resident ? bres + (uint32_t)c * bstep : da + boff;
         if (elect_one()) {
           const uint32_t acc0 = (uint32_t)(c != 0);
           if (nk == 4) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16_lh(tmem_d, da + 2u * k, da + boff + 2u * k, hi32, G.idesc, k ? 1u : acc0);
+            for (int k = 0; k < 4; ++k) umma_bf16_lh(tmem_d, da + 2u * k, db + 2u * k, hi32, G.idesc, k ? 1u : acc0);
           } else if (nk == 2) {
 #pragma unroll
-            for (int k = 0; k < 2; ++k) umma_bf16_lh(tmem_d, da + 2u * k, da + boff + 2u * k, hi32, G.idesc, k ? 1u : acc0);
+            for (int k = 0; k < 2; ++k) umma_bf16_lh(tmem_d, da + 2u * k, db + 2u * k, hi32, G.idesc, k ? 1u : acc0);
           } else {
-            umma_bf16_lh(tmem_d, da, da + boff, hi32, G.idesc, acc0);
+            umma_bf16_lh(tmem_d, da, db, hi32, G.idesc, acc0);
           }
           umma_commit(bar_empty0 + 8u * s);   // frees the smem stage once these MMAs retire
         }
@@ -163,10 +190,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     const int c_end = (kEpiWarps == 8) ? (half == 0 ? (nchunks + 1) / 2 : nchunks) : nchunks;
     const bool store_thread = (warp == 2 && lane == 0);
     int it = 0;
-    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
+    for (int t = t_first; t < t_end; t += t_step, ++it) {
       const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
-      const int n_tile = t % G.tiles_n;
-      int m_tile = t / G.tiles_n;
+      const int n_tile = G.resident ? res_n : t % G.tiles_n;
+      int m_tile = G.resident ? t : t / G.tiles_n;
       const int img = m_tile / tiles_m_per_img;
       m_tile -= img * tiles_m_per_img;
       const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
@@ -204,29 +231,67 @@ struct ConvTcPlan {
   ConvTcArgs args;
   int grid;
   size_t smem;
+  void* w_repack = nullptr;   // pair-view weights owned by the plan (stride-2, 32-channel inputs)
+  ~ConvTcPlan() { if (w_repack) cudaFree(w_repack); }
 };
 
-// Tile-N heuristic: estimated cycles = rounds of the persistent grid x per-tile cost, where a tile costs
-// max(MMA issue, operand bytes / ~42 B/clk/SM of L2->smem TMA throughput, epilogue) -- see DESIGN.md.
-static int pick_tile_n(int cout, long long m_tiles, int chunks, int bk, bool out_f32) {
-  if (cout <= 32) return 32;
-  const int cands[3] = {64, 128, 256};
-  int best = 64;
+constexpr size_t kAuxBytes = 8 * (2 * 12 + 6) + 16 + (size_t)kMaxBias * 4 + 64;
+
+static size_t tile_smem(int bn, int bk, int y_es, bool resident, int chunks, int stages) {
+  const size_t a = (size_t)128 * bk * 2, b = (size_t)bn * bk * 2;
+  const size_t out = ((size_t)bn * y_es + 127) / 128 * 16384;
+  return 1024 + (resident ? b * chunks + a * stages : (a + b) * stages) + out + kAuxBytes;
+}
+
+// Tile-N / weight-residency heuristic: estimated cycles = rounds of the persistent grid x per-tile cost, where a
+// tile costs max(MMA issue, operand bytes / ~42 B/clk/SM of L2->smem throughput, epilogue).  With resident
+// weights the per-tile operand bytes are the activations only and the weights are fetched once per CTA.
+static void pick_tile(int cout, long long m_tiles, int chunks, int bk, int y_es, int* bn_out, int* resident_out) {
+  const int cands[4] = {32, 64, 128, 256};
+  static const char* force_env = getenv("YB_RESIDENT");   // tuning aid: 0 = never, 1 = whenever it fits
+  const int force = force_env ? atoi(force_env) : -1;
+  int best = 64, best_res = 0;
   double best_cost = 1e30;
-  for (int i = 0; i < 3; ++i) {
+  for (int i = 0; i < 4; ++i) {
     const int bn = cands[i];
-    if (out_f32 && bn > 128) continue;  // fp32 staging tile would not leave room for the pipeline
-    const long long tiles = m_tiles * ((cout + bn - 1) / bn);
-    const double rounds = (double)((tiles + num_sms() - 1) / num_sms());
-    const double mma = chunks * (bk / 16) * (bn / 2.0);
-    const double load = chunks * (128.0 * bk * 2 + (double)bn * bk * 2) / 42.0;
-    const double epi = bn * 10.0 + 600.0;
-    double tile = mma > load ? mma : load;
-    if (epi > tile) tile = epi;
-    const double cost = rounds * (tile + 400.0);
-    if (cost < best_cost * 0.999) { best_cost = cost; best = bn; }
+    if (bn == 32 && cout > 32) continue;
+    if (bn > 32 && cout <= 32) continue;
+    if (y_es == 4 && bn > 128) continue;  // fp32 staging tile would not leave room for the pipeline
+    const int tiles_n = (cout + bn - 1) / bn;
+    for (int res = 0; res < 2; ++res) {
+      if (force == 0 && res) continue;
+      if (res && tiles_n != 1) continue;   // measured: splitting Cout to make the weights fit re-reads A and loses
+      if (res && (tile_smem(bn, bk, y_es, true, chunks, 4) > 227 * 1024 || tiles_n > num_sms())) continue;
+      if (!res && tile_smem(bn, bk, y_es, false, chunks, 2) > 227 * 1024) continue;
+      const long long tiles = m_tiles * tiles_n;
+      int grid = (int)(tiles < num_sms() ? tiles : num_sms());
+      if (res) grid = grid / tiles_n * tiles_n;
+      if (grid < 1) continue;
+      const double rounds = (double)((tiles + grid - 1) / grid);
+      const double mma = chunks * (bk / 16) * (bn / 2.0);
+      const double a_b = 128.0 * bk * 2, b_b = (double)bn * bk * 2;
+      const double load = chunks * (a_b + (res ? 0.0 : b_b)) / 42.0;
+      const double epi = bn * 10.0 + 600.0;
+      double tile = mma > load ? mma : load;
+      if (epi > tile) tile = epi;
+      const double cost = rounds * (tile + 400.0) + (res ? chunks * b_b / 42.0 : 0.0);
+      if (force == 1 && res) { const double c1 = cost * 1e-6; if (c1 < best_cost) { best_cost = c1; best = bn; best_res = 1; } continue; }
+      if (cost < best_cost * 0.999) { best_cost = cost; best = bn; best_res = res; }
+    }
   }
-  return best;
+  *bn_out = best; *resident_out = best_res;
+}
+
+// [Cout_pad][9][cin_pad] (Cin = 32) -> [Cout_pad][3 dy][2 pair taps][64]: a stride-2 3x3 conv over 32-channel pixels
+// read as a (3 x 2, stride 2 x 1) conv over 64-channel pixel PAIRS: pair tap 0 = (zeros | dx 0) of pair ox - 1,
+// pair tap 1 = (dx 1 | dx 2) of pair ox.  128-byte TMA rows instead of 64-byte ones, 6 taps instead of 9.
+__global__ void k_repack_pair(const __nv_bfloat16* w, int cin_pad, int cout_pad, __nv_bfloat16* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cout_pad * 6 * 64) return;
+  const int ch = i & 63, pt = (i >> 6) % 2, dy = (i >> 7) % 3, co = i / 384;
+  const int c = ch & 31, hi = ch >> 5;
+  const int dx = pt == 0 ? (hi ? 0 : -1) : (hi ? 2 : 1);
+  out[i] = dx < 0 ? __float2bfloat16_rn(0.f) : w[((size_t)co * 9 + dy * 3 + dx) * cin_pad + c];
 }
 
 int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
@@ -242,17 +307,32 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
                "conv(tc): output channel stride must be a multiple of 16 bytes");
   const int k = d.k, s = d.stride, pad = k / 2, ups = d.upsample;
   const int Ho = (x.H + 2 * pad - k) / s + 1, Wo = (x.W + 2 * pad - k) / s + 1;
-  const int Cin = x.C, Cout = y.C;
+  const int Cout = y.C;
   ConvTcPlan* P = new ConvTcPlan();
   ConvTcArgs& A = P->args;
   memset(&A, 0, sizeof(A));
   A.bias = d.bias; A.bias_len = d.cout_pad;
-  A.ksz = k; A.taps = k * k; A.stride = s; A.pad = pad;
+  // pair view (see k_repack_pair): needs pixel pairs to be contiguous in memory
+  const bool pair = k == 3 && s == 2 && x.C == 32 && x.c_stride == 32 && x.W % 2 == 0 && ups == 1 && d.tile_n >= 0;
+  int Cin = x.C, cin_pad = d.cin_pad, xW = x.W, x_cs = x.c_stride;
+  int kh = k, kw = k, sh = s, sw = s, ph = pad, pw = pad;
+  const void* weight = d.weight;
+  if (pair) {
+    Cin = 64; cin_pad = 64; xW = x.W / 2; x_cs = 64;
+    kh = 3; kw = 2; sh = 2; sw = 1; ph = 1; pw = 1;
+    const size_t n = (size_t)d.cout_pad * 6 * 64;
+    if (cudaMalloc(&P->w_repack, n * 2) != cudaSuccess) { delete P; set_error("conv(tc): cudaMalloc failed"); return YB_ERR_CUDA; }
+    k_repack_pair<<<(int)((n + 255) / 256), 256>>>((const __nv_bfloat16*)d.weight, d.cin_pad, d.cout_pad,
+                                                   (__nv_bfloat16*)P->w_repack);
+    if (cudaDeviceSynchronize() != cudaSuccess) { delete P; set_error("conv(tc): weight repack failed"); return YB_ERR_CUDA; }
+    weight = P->w_repack;
+  }
+  A.kw = kw; A.taps = kh * kw; A.stride_h = sh; A.stride_w = sw; A.pad_h = ph; A.pad_w = pw;
   A.act = d.act; A.slope = d.leaky_slope;
   A.out_f32 = y.dtype == YB_F32;
   A.BK = Cin >= 64 ? 64 : (Cin >= 32 ? 32 : 16);
-  if (A.BK > d.cin_pad) A.BK = d.cin_pad >= 32 ? 32 : 16;
-  YB_CHECK_ARG(d.cin_pad >= 16, "conv(tc): cin_pad must be >= 16");
+  if (A.BK > cin_pad) A.BK = cin_pad >= 32 ? 32 : 16;
+  YB_CHECK_ARG(cin_pad >= 16, "conv(tc): cin_pad must be >= 16");
   A.kchunks = (Cin + A.BK - 1) / A.BK;
   A.sw_mode = A.BK == 64 ? 2 : (A.BK == 32 ? 4 : 6);
   const CUtensorMapSwizzle sw_in = A.BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
@@ -269,7 +349,7 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
     for (int bw = 1; bw <= 128 && bw <= Wo; ++bw) {
       int bh = 128 / bw;
       if (bh > Ho) bh = Ho;
-      if (bh * s > 256 || bw * s > 256) continue;
+      if (bh * sh > 256 || bw * sw > 256) continue;
       int cost = ((Wo + bw - 1) / bw) * ((Ho + bh - 1) / bh);
       if (cost < best_cost || (cost == best_cost && bw > best_bw)) { best_cost = cost; best_bw = bw; }
     }
@@ -278,23 +358,28 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
     A.tiles_w = (Wo + A.BW - 1) / A.BW;
     A.tiles_h = (Ho + A.BH - 1) / A.BH;
   }
-  A.BN = d.tile_n ? d.tile_n : pick_tile_n(Cout, (long long)A.tiles_w * A.tiles_h * images, A.taps * A.kchunks, A.BK,
-                                          y.dtype == YB_F32);
+  const int total_chunks = A.taps * A.kchunks;
+  if (d.tile_n) {
+    A.BN = d.tile_n < 0 ? -d.tile_n : d.tile_n;
+    A.resident = 0;
+    if (A.BN == 1) pick_tile(Cout, (long long)A.tiles_w * A.tiles_h * images, total_chunks, A.BK, y_es, &A.BN, &A.resident);
+  } else {
+    pick_tile(Cout, (long long)A.tiles_w * A.tiles_h * images, total_chunks, A.BK, y_es, &A.BN, &A.resident);
+  }
   YB_CHECK_ARG(A.BN == 32 || A.BN == 64 || A.BN == 128 || A.BN == 256, "conv(tc): tile_n must be 32/64/128/256");
   A.tiles_n = (Cout + A.BN - 1) / A.BN;
   A.n_store_maps = ups == 2 ? 4 : 1;
   A.tmem_cols = 2 * A.BN < 32 ? 32 : 2 * A.BN;   // double-buffered accumulators (64/128/256/512 columns)
   A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
   // stages / shared memory
-  const size_t stage_bytes = (size_t)128 * A.BK * 2 + (size_t)A.BN * A.BK * 2;
-  const size_t stage_out = ((size_t)A.BN * y_es + 127) / 128 * 16384;
-  const size_t aux_bytes = 8 * (2 * 12 + 4) + 16 + (size_t)kMaxBias * 4 + 64;
-  const size_t budget = 226 * 1024 - 1024 - stage_out - aux_bytes;
-  int stages = d.stages ? d.stages : (int)(budget / stage_bytes);
+  const size_t a_stage = (size_t)128 * A.BK * 2, b_tile = (size_t)A.BN * A.BK * 2;
+  const size_t stage_bytes = A.resident ? a_stage : a_stage + b_tile;
+  const size_t fixed = tile_smem(A.BN, A.BK, y_es, A.resident != 0, total_chunks, 0);
+  int stages = d.stages ? d.stages : (int)((226 * 1024 - fixed) / stage_bytes);
   if (stages > 12) stages = 12;
   if (stages < 2) stages = 2;
   A.stages = stages;
-  P->smem = 1024 + stage_bytes * stages + stage_out + aux_bytes;
+  P->smem = fixed + stage_bytes * stages;
   YB_CHECK_ARG(d.cout_pad <= kMaxBias, "conv(tc): cout_pad > %d unsupported", kMaxBias);
   if (P->smem > 227 * 1024) {
     set_error("conv(tc): shared memory budget exceeded (%zu bytes)", P->smem);
@@ -306,8 +391,8 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   // ---- A: activations
   {
     uint64_t dims[4], str[3];
-    uint32_t box[4], es[4] = {1, (uint32_t)s, (uint32_t)s, 1};
-    const uint64_t cs = (uint64_t)x.c_stride * 2;
+    uint32_t box[4], es[4] = {1, (uint32_t)sw, (uint32_t)sh, 1};
+    const uint64_t cs = (uint64_t)x_cs * 2;
     if (A.flat) {
       const uint64_t M = (uint64_t)x.N * x.H * x.W;
       dims[0] = Cin; dims[1] = M; dims[2] = 1; dims[3] = 1;
@@ -315,19 +400,19 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
       box[0] = A.BK; box[1] = 128; box[2] = 1; box[3] = 1;
       es[1] = es[2] = 1;
     } else {
-      dims[0] = Cin; dims[1] = x.W; dims[2] = x.H; dims[3] = x.N;
-      str[0] = cs; str[1] = cs * x.W; str[2] = cs * x.W * x.H;
-      box[0] = A.BK; box[1] = A.BW * s; box[2] = A.BH * s; box[3] = 1;
+      dims[0] = Cin; dims[1] = xW; dims[2] = x.H; dims[3] = x.N;
+      str[0] = cs; str[1] = cs * xW; str[2] = cs * xW * x.H;
+      box[0] = A.BK; box[1] = A.BW * sw; box[2] = A.BH * sh; box[3] = 1;
     }
     rc = encode(&A.tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x.data, dims, str, box, es, sw_in, "activations");
     if (rc) { delete P; return rc; }
   }
   // ---- B: weights [cout_pad][taps][cin_pad]
   {
-    uint64_t dims[3] = {(uint64_t)d.cin_pad, (uint64_t)A.taps, (uint64_t)d.cout_pad};
-    uint64_t str[2] = {(uint64_t)d.cin_pad * 2, (uint64_t)d.cin_pad * 2 * A.taps};
+    uint64_t dims[3] = {(uint64_t)cin_pad, (uint64_t)A.taps, (uint64_t)d.cout_pad};
+    uint64_t str[2] = {(uint64_t)cin_pad * 2, (uint64_t)cin_pad * 2 * A.taps};
     uint32_t box[3] = {(uint32_t)A.BK, 1, (uint32_t)A.BN};
-    rc = encode(&A.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, d.weight, dims, str, box, one4, sw_in, "weights");
+    rc = encode(&A.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, weight, dims, str, box, one4, sw_in, "weights");
     if (rc) { delete P; return rc; }
   }
   // ---- Y: outputs (swizzle-128B staging, 128-byte inner box)
@@ -362,6 +447,7 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   YB_CHECK_ARG(grid < 0x7fffffffLL, "conv(tc): grid too large");
   A.total_tiles = (int)grid;
   P->grid = (int)(grid < num_sms() ? grid : num_sms());
+  if (A.resident) P->grid = P->grid / A.tiles_n * A.tiles_n;
   *out = P;
   return YB_OK;
 }
@@ -372,8 +458,7 @@ int conv_tc_launch(const ConvTcPlan* P, cudaStream_t s) {
     YB_CUDA(cudaFuncSetAttribute(k_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  k_conv_tc<<<P->grid, kTcThreads, P->smem, s>>>(P->args);
-  YB_LAUNCH_CHECK();
+  YB_CUDA(launch_pdl(k_conv_tc, P->grid, kTcThreads, P->smem, s, P->args));
   return YB_OK;
 }
 
@@ -412,4 +497,37 @@ extern "C" int yb_conv2d(const yb_conv_desc* d, void* stream) {
   rc = conv_tc_launch(p, (cudaStream_t)stream);
   conv_tc_plan_destroy(p);
   return rc;
+}
+
+// ---- reusable single-conv plans (tensor maps encoded once; yb_conv2d re-encodes them on every call)
+struct yb_conv_plan {
+  yb::ConvTcPlan* tc = nullptr;
+  yb::Conv3Plan* c3 = nullptr;
+};
+
+extern "C" int yb_conv_plan_create(const yb_conv_desc* d, yb_conv_plan** out) {
+  YB_CHECK_ARG(d && out && view_ok(d->x) && view_ok(d->y) && d->weight && d->bias, "yb_conv_plan_create: bad descriptor");
+  YB_CHECK_ARG(d->x.dtype == YB_BF16, "yb_conv_plan_create: bf16 activations only");
+  YB_CHECK_ARG((d->k == 1 || d->k == 3) && (d->stride == 1 || d->stride == 2), "yb_conv_plan_create: k in {1,3}, stride in {1,2}");
+  yb_conv_desc dd = *d;
+  yb_conv_plan* p = new yb_conv_plan();
+  int rc = YB_ERR_UNSUPPORTED;
+  if (dd.tile_n >= 0) rc = conv3_tc_plan_create(dd, &p->c3);
+  else dd.tile_n = dd.tile_n == -1 ? 0 : -dd.tile_n;
+  if (rc == YB_ERR_UNSUPPORTED) rc = conv_tc_plan_create(dd, &p->tc);
+  if (rc != YB_OK) { delete p; return rc; }
+  *out = p;
+  return YB_OK;
+}
+
+extern "C" int yb_conv_plan_launch(const yb_conv_plan* p, void* stream) {
+  YB_CHECK_ARG(p && (p->tc || p->c3), "yb_conv_plan_launch: null plan");
+  return p->c3 ? conv3_tc_launch(p->c3, (cudaStream_t)stream) : conv_tc_launch(p->tc, (cudaStream_t)stream);
+}
+
+extern "C" void yb_conv_plan_destroy(yb_conv_plan* p) {
+  if (!p) return;
+  if (p->tc) conv_tc_plan_destroy(p->tc);
+  if (p->c3) conv3_tc_plan_destroy(p->c3);
+  delete p;
 }

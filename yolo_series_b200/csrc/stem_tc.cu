@@ -136,6 +136,8 @@ __global__ void __launch_bounds__(kStThreads, 3) k_stem_tc(const StemTcParams P)
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();   // the image (and the output buffer's previous readers) belong to earlier work in the stream
 
   if (warp == 0) {
     // ================================ MMA issuer ==================================
@@ -322,8 +324,7 @@ int launch_one(const StemTcParams& P, int grid, cudaStream_t st) {
     YB_CUDA(cudaFuncSetAttribute(k_stem_tc<S, U8, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  k_stem_tc<S, U8, ACT><<<grid, kStThreads, smem, st>>>(P);
-  YB_LAUNCH_CHECK();
+  YB_CUDA(launch_pdl(k_stem_tc<S, U8, ACT>, grid, kStThreads, smem, st, P));
   return YB_OK;
 }
 

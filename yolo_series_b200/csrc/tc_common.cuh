@@ -180,6 +180,14 @@ __device__ __forceinline__ void epi_chunks_dispatch(int act, uint32_t taddr, int
   else epi_chunks<YB_ACT_NONE>(taddr, c_begin, c_end, bias_n0, slope, staging, row, xr, out_f32);
 }
 
+// Programmatic dependent launch: a kernel launched with launch_pdl() may start while its predecessor in the
+// stream is still draining.  Everything before pdl_wait() must only touch memory no earlier kernel writes
+// (weights, bias, tensor maps, shared memory / TMEM set-up); pdl_wait() returns once the predecessor has
+// completed and its writes are visible.  pdl_launch_dependents() lets the successor's CTAs be scheduled as
+// soon as SM resources free up.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // One elected lane of a fully converged warp.  The surrounding control flow stays warp-uniform, so
 // descriptor / address arithmetic is done once on the uniform datapath instead of per MMA via R2UR.
 __device__ __forceinline__ bool elect_one() {
