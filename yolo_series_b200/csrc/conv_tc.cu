@@ -13,6 +13,8 @@
 // (tcgen05.ld -> +bias -> SiLU/LeakyReLU -> bf16/fp32 -> swizzled smem -> TMA store).  The store
 // tensor map addresses a channel slice of the consumer's concat buffer (Concat fused away) and, for
 // convs feeding nn.Upsample, four maps with doubled strides write the 2x2 replicas.
+#include <type_traits>
+
 #include "tc_common.cuh"
 
 namespace yb {
@@ -25,6 +27,7 @@ struct ConvTcArgs {
   int tiles_n, tiles_w, tiles_h;   // tile grid; m tiles = tiles_w * tiles_h * images
   int BW, BH, BN, BK;              // spatial box, N tile, K chunk (channels)
   int taps, kw, stride_h, stride_w, pad_h, pad_w;   // taps = kh * kw, tap = dy * kw + dx
+  int epi_ring, epi_cpr;           // output staging ring (in rounds) and 32-column chunks per warp per round
   int resident;                    // 1: all weight tiles of the CTA's N tile stay in shared memory
   int kchunks;                     // ceil(Cin / BK)
   int stages;
@@ -55,10 +58,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   const uint32_t res_bytes = G.resident ? b_bytes * (uint32_t)(G.taps * G.kchunks) : 0u;
   const uint32_t stage_bytes = G.resident ? a_bytes : a_bytes + b_bytes;
   const uint32_t ring = tiles + res_bytes;
-  const uint32_t out_es = G.out_f32 ? 4u : 2u;
   const uint32_t pipe_bytes = res_bytes + stage_bytes * G.stages;
   const uint32_t staging = tiles + pipe_bytes;                       // 1024-aligned (all pieces are multiples of 1024)
-  const uint32_t staging_bytes = ((uint32_t)G.BN * out_es + 127u) / 128u * 16384u;   // 128 rows x 128 B per group
+  const uint32_t round_bytes = (G.out_f32 ? 32768u : 16384u) * (uint32_t)G.epi_cpr;
+  const uint32_t staging_bytes = round_bytes * (uint32_t)G.epi_ring;
   unsigned char* aux = tiles_ptr + pipe_bytes + staging_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(aux);  // full[S], empty[S], tmem_full[2], tmem_empty[2], resident
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux + 8 * (2 * G.stages + 6));
@@ -186,37 +189,77 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     const int row = q * 32 + lane;
     const uint32_t xr = (uint32_t)(row & 7);
     const int nchunks = G.BN / 32;
-    const int c_begin = (kEpiWarps == 8) ? (half * ((nchunks + 1) / 2)) : 0;
-    const int c_end = (kEpiWarps == 8) ? (half == 0 ? (nchunks + 1) / 2 : nchunks) : nchunks;
+    // A round = every epilogue warp converts G.epi_cpr 32-column chunks (the two warps of a lane quarter take the
+    // even / odd chunks), followed by one barrier and the TMA store of the round's columns from a ring slot.
+    const int cpr = G.epi_cpr;
+    const int nrounds = (nchunks + 2 * cpr - 1) / (2 * cpr);
+    const uint32_t round_cols = 64u * (uint32_t)cpr;
     const bool store_thread = (warp == 2 && lane == 0);
-    int it = 0;
-    for (int t = t_first; t < t_end; t += t_step, ++it) {
-      const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
-      const int n_tile = G.resident ? res_n : t % G.tiles_n;
-      int m_tile = G.resident ? t : t / G.tiles_n;
-      const int img = m_tile / tiles_m_per_img;
-      m_tile -= img * tiles_m_per_img;
-      const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
-      const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
-      mbar_wait(bar_tfull0 + 8u * acc, aph);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging free again
-      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)G.BN;
-      epi_chunks_dispatch(G.act, taddr, c_begin, c_end, bias_s + n0, G.slope, staging, row, xr, G.out_f32 != 0);
-      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to TMA
-      asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
-      if (store_thread) {
-        mbar_arrive(bar_tempty0 + 8u * acc);   // every epilogue warp has finished reading this accumulator
-        const int per_group = G.out_f32 ? 32 : 64;
-        const int ngroups = (G.BN + per_group - 1) / per_group;
-        for (int mp = 0; mp < G.n_store_maps; ++mp)
-          for (int g = 0; g < ngroups; ++g)
-            tma_store_4d(&G.tm_y[mp], staging + (uint32_t)g * 16384u, n0 + g * per_group, w0, G.flat ? 0 : h0, img);
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    // The activation is a compile-time constant inside the loop (straight-line element code).
+    auto run = [&](auto act_c) {
+      constexpr int ACT = decltype(act_c)::value;
+      uint32_t slot = 0;
+      int it = 0;
+      for (int t = t_first; t < t_end; t += t_step, ++it) {
+        const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
+        const int n_tile = G.resident ? res_n : t % G.tiles_n;
+        int m_tile = G.resident ? t : t / G.tiles_n;
+        const int img = m_tile / tiles_m_per_img;
+        m_tile -= img * tiles_m_per_img;
+        const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+        const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
+        mbar_wait(bar_tfull0 + 8u * acc, aph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)G.BN;
+        for (int r = 0; r < nrounds; ++r) {
+          const uint32_t sbase = staging + slot * round_bytes;
+          if (G.epi_ring == 1) {   // single slot: wait (lazily) until the previous store has read it
+            if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+          }
+          for (int u = 0; u < cpr; ++u) {
+            const int cc = 2 * cpr * r + 2 * u + half;
+            if (cc < nchunks) {
+              uint32_t v[32];
+              tmem_ld32(taddr + (uint32_t)(cc * 32), v);
+              const float* bs = bias_s + n0 + cc * 32;
+              if (G.out_f32) epi_chunk_f32<ACT>(v, bs, G.slope, sbase + (uint32_t)(2 * u + half) * 16384u + (uint32_t)row * 128u, xr);
+              else epi_chunk_bf16<ACT>(v, bs, G.slope, sbase + (uint32_t)u * 16384u + (uint32_t)row * 128u, (uint32_t)half, xr);
+            }
+          }
+          if (r == nrounds - 1) asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to TMA
+          // Before the barrier releases the next round onto the next ring slot, its previous store must have
+          // finished reading it: that store is ring - 1 commits back, and this round's is not committed yet.
+          if (store_thread) {
+            if (G.epi_ring >= 4) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+            else if (G.epi_ring == 3) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            else if (G.epi_ring == 2) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+          if (store_thread) {
+            if (r == nrounds - 1) mbar_arrive(bar_tempty0 + 8u * acc);   // every warp has read this accumulator
+            const int col0 = n0 + (int)round_cols * r;
+            for (int mp = 0; mp < G.n_store_maps; ++mp) {
+              if (G.out_f32) {   // 32-column slots
+                for (int j = 0; j < 2 * cpr; ++j)
+                  if (2 * cpr * r + j < nchunks)
+                    tma_store_4d(&G.tm_y[mp], sbase + (uint32_t)j * 16384u, col0 + 32 * j, w0, G.flat ? 0 : h0, img);
+              } else {           // 64-column slots
+                for (int u = 0; u < cpr; ++u)
+                  if (2 * cpr * r + 2 * u < nchunks)
+                    tma_store_4d(&G.tm_y[mp], sbase + (uint32_t)u * 16384u, col0 + 64 * u, w0, G.flat ? 0 : h0, img);
+              }
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          slot = slot + 1 == (uint32_t)G.epi_ring ? 0u : slot + 1;
+        }
       }
-    }
+    };
+    if (G.act == YB_ACT_SILU) run(std::integral_constant<int, YB_ACT_SILU>{});
+    else if (G.act == YB_ACT_LEAKY) run(std::integral_constant<int, YB_ACT_LEAKY>{});
+    else run(std::integral_constant<int, YB_ACT_NONE>{});
     if (store_thread) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   __syncthreads();
@@ -237,9 +280,12 @@ struct ConvTcPlan {
 
 constexpr size_t kAuxBytes = 8 * (2 * 12 + 6) + 16 + (size_t)kMaxBias * 4 + 64;
 
-static size_t tile_smem(int bn, int bk, int y_es, bool resident, int chunks, int stages) {
+// one round per tile: each epilogue warp converts half of the tile's 32-column chunks
+static int epi_cpr_for(int bn, int y_es) { (void)y_es; return (bn / 32 + 1) / 2; }
+
+static size_t tile_smem(int bn, int bk, int y_es, bool resident, int chunks, int stages, int ring = 1) {
   const size_t a = (size_t)128 * bk * 2, b = (size_t)bn * bk * 2;
-  const size_t out = ((size_t)bn * y_es + 127) / 128 * 16384;
+  const size_t out = (size_t)ring * (y_es == 4 ? 32768 : 16384) * epi_cpr_for(bn, y_es);
   return 1024 + (resident ? b * chunks + a * stages : (a + b) * stages) + out + kAuxBytes;
 }
 
@@ -353,6 +399,8 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
       int cost = ((Wo + bw - 1) / bw) * ((Ho + bh - 1) / bh);
       if (cost < best_cost || (cost == best_cost && bw > best_bw)) { best_cost = cost; best_bw = bw; }
     }
+    static const char* bw_env = getenv("YB_TILE_BW");   // tuning aid
+    if (bw_env && atoi(bw_env) > 0 && atoi(bw_env) <= 128) best_bw = atoi(bw_env);
     A.BW = best_bw;
     A.BH = 128 / best_bw < Ho ? 128 / best_bw : Ho;
     A.tiles_w = (Wo + A.BW - 1) / A.BW;
@@ -374,7 +422,21 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   // stages / shared memory
   const size_t a_stage = (size_t)128 * A.BK * 2, b_tile = (size_t)A.BN * A.BK * 2;
   const size_t stage_bytes = A.resident ? a_stage : a_stage + b_tile;
-  const size_t fixed = tile_smem(A.BN, A.BK, y_es, A.resident != 0, total_chunks, 0);
+  // output staging ring: deep enough to overlap the TMA store of one round with the next round's math, as long
+  // as the operand pipeline keeps at least 4 stages
+  A.epi_cpr = epi_cpr_for(A.BN, y_es);
+  // A deeper ring overlaps a tile's TMA store with the next tile's epilogue math: worth its shared memory for
+  // short-K layers (the epilogue is the critical path), not when it would thin out the operand pipeline.
+  int ring = 3;
+  size_t fixed = 0;
+  for (; ring >= 1; --ring) {
+    fixed = tile_smem(A.BN, A.BK, y_es, A.resident != 0, total_chunks, 0, ring);
+    if (ring == 1) break;
+    if (fixed >= 226 * 1024) continue;
+    const int st = (int)((226 * 1024 - fixed) / stage_bytes);
+    if (st >= 8 || (total_chunks <= 4 && st >= 4)) break;
+  }
+  A.epi_ring = ring;
   int stages = d.stages ? d.stages : (int)((226 * 1024 - fixed) / stage_bytes);
   if (stages > 12) stages = 12;
   if (stages < 2) stages = 2;
