@@ -173,6 +173,7 @@ def lower(layers, in_ch=3, fused=False, keep_aux=False):
     _fuse_sp_triples(L)
     _fuse_upsample(L)
     _drop_dead(L)
+    _merge_sibling_convs(L)
     return L
 
 
@@ -205,6 +206,43 @@ def _fuse_upsample(L):
         prod.upsample = 2
         prod.name += '+up2'
         L.ops.remove(up)
+
+
+def _merge_sibling_convs(L):
+    """Two 1x1/s1 convs that read the same tensor and write neighbouring channel slices of one concat buffer
+    (the cv1 / cv2 pair that opens every ELAN block, cfg/deploy/yolov7.yaml nodes 4-5, 17-18, ...) become one
+    conv with the filters stacked: the input is read once and one kernel is launched.  Per output channel the
+    arithmetic is unchanged, so results are bit-identical."""
+    import torch
+    i = 0
+    while i < len(L.ops):
+        a = L.ops[i]
+        i += 1
+        if a.kind != OP_CONV or a.conv.k != 1 or a.conv.s != 1 or a.upsample != 1:
+            continue
+        va = L.vals[a.outs[0]]
+        if va.parent is None or va.f32:
+            continue
+        for b in L.ops[i:]:
+            if b.kind != OP_CONV or b.ins != a.ins or b.conv.k != 1 or b.conv.s != 1 or b.upsample != 1:
+                continue
+            vb = L.vals[b.outs[0]]
+            if vb.parent != va.parent or vb.f32 or (b.conv.act, b.conv.slope) != (a.conv.act, a.conv.slope):
+                continue
+            if va.offset + va.C == vb.offset:
+                lo, hi, vlo = a, b, va
+            elif vb.offset + vb.C == va.offset:
+                lo, hi, vlo = b, a, vb
+            else:
+                continue
+            fc = fold.FoldedConv(torch.cat([lo.conv.weight, hi.conv.weight], 0), torch.cat([lo.conv.bias, hi.conv.bias], 0),
+                                 1, 1, a.conv.act, a.conv.slope)
+            merged = Val(len(L.vals), va.C + vb.C, va.num, va.den, parent=va.parent, offset=vlo.offset)
+            L.vals.append(merged)
+            a.conv, a.outs, a.name = fc, [merged.vid], lo.name + '+' + hi.name
+            L.vals[a.ins[0]].users -= 1
+            L.ops.remove(b)
+            break
 
 
 def _drop_dead(L):
