@@ -41,6 +41,10 @@ CONV_CASES = [
     (2, 40, 40, 128, 128, 3, 1, 1, 1),      # slab kernel, 40-wide map (120-pixel sub-tiles)
     (1, 80, 80, 64, 192, 3, 1, 1, 1),       # slab kernel, 16x8 sub-tiles, 3 N tiles of 64
     (2, 24, 24, 512, 64, 3, 1, 1, 1),       # slab kernel, 8 K chunks
+    (2, 128, 192, 32, 64, 3, 2, 1, 1),      # pair-slab stride-2 kernel (Cin 32), several tiles per image
+    (1, 36, 52, 32, 64, 3, 2, 1, 1),        # pair-slab, ragged tiles in both directions
+    (1, 32, 64, 32, 32, 3, 2, 2, 1),        # pair-slab, Cout 32, LeakyReLU
+    (1, 35, 52, 32, 64, 3, 2, 1, 1),        # odd height: generic kernel with the pair view
 ]
 
 

@@ -101,6 +101,11 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out);
 int conv3_tc_launch(const Conv3Plan* p, cudaStream_t s);
 void conv3_tc_plan_destroy(Conv3Plan* p);
 
+struct ConvS2pPlan;  // 3x3 stride-2 pair-slab kernel for 32-channel inputs (conv3s2p_tc.cu)
+int conv3s2p_plan_create(const yb_conv_desc& d, ConvS2pPlan** out);
+int conv3s2p_launch(const ConvS2pPlan* p, cudaStream_t s);
+void conv3s2p_plan_destroy(ConvS2pPlan* p);
+
 // tcgen05 first layer for 3-channel images (stem_tc.cu); YB_ERR_UNSUPPORTED -> caller uses the mma.sync stem
 int stem_tc_launch(const void* img, int img_u8, int B, int H, int W, const void* weight, const float* bias,
                    int cin_pad, int stride, int act, float slope, const yb_tensor* y, cudaStream_t st);

@@ -550,6 +550,14 @@ extern "C" int yb_conv2d(const yb_conv_desc* d, void* stream) {
       return rc3;
     }
     if (rc3 != YB_ERR_UNSUPPORTED) return rc3;
+    ConvS2pPlan* ps = nullptr;
+    rc3 = conv3s2p_plan_create(dd, &ps);
+    if (rc3 == YB_OK) {
+      rc3 = conv3s2p_launch(ps, (cudaStream_t)stream);
+      conv3s2p_plan_destroy(ps);   // cudaFree of the repacked weights waits for the kernel
+      return rc3;
+    }
+    if (rc3 != YB_ERR_UNSUPPORTED) return rc3;
   } else {
     dd.tile_n = dd.tile_n == -1 ? 0 : -dd.tile_n;
   }
@@ -565,6 +573,7 @@ extern "C" int yb_conv2d(const yb_conv_desc* d, void* stream) {
 struct yb_conv_plan {
   yb::ConvTcPlan* tc = nullptr;
   yb::Conv3Plan* c3 = nullptr;
+  yb::ConvS2pPlan* s2p = nullptr;
 };
 
 extern "C" int yb_conv_plan_create(const yb_conv_desc* d, yb_conv_plan** out) {
@@ -575,6 +584,7 @@ extern "C" int yb_conv_plan_create(const yb_conv_desc* d, yb_conv_plan** out) {
   yb_conv_plan* p = new yb_conv_plan();
   int rc = YB_ERR_UNSUPPORTED;
   if (dd.tile_n >= 0) rc = conv3_tc_plan_create(dd, &p->c3);
+  if (rc == YB_ERR_UNSUPPORTED && dd.tile_n >= 0) rc = conv3s2p_plan_create(dd, &p->s2p);
   else dd.tile_n = dd.tile_n == -1 ? 0 : -dd.tile_n;
   if (rc == YB_ERR_UNSUPPORTED) rc = conv_tc_plan_create(dd, &p->tc);
   if (rc != YB_OK) { delete p; return rc; }
@@ -583,7 +593,8 @@ extern "C" int yb_conv_plan_create(const yb_conv_desc* d, yb_conv_plan** out) {
 }
 
 extern "C" int yb_conv_plan_launch(const yb_conv_plan* p, void* stream) {
-  YB_CHECK_ARG(p && (p->tc || p->c3), "yb_conv_plan_launch: null plan");
+  YB_CHECK_ARG(p && (p->tc || p->c3 || p->s2p), "yb_conv_plan_launch: null plan");
+  if (p->s2p) return conv3s2p_launch(p->s2p, (cudaStream_t)stream);
   return p->c3 ? conv3_tc_launch(p->c3, (cudaStream_t)stream) : conv_tc_launch(p->tc, (cudaStream_t)stream);
 }
 
@@ -591,5 +602,6 @@ extern "C" void yb_conv_plan_destroy(yb_conv_plan* p) {
   if (!p) return;
   if (p->tc) conv_tc_plan_destroy(p->tc);
   if (p->c3) conv3_tc_plan_destroy(p->c3);
+  if (p->s2p) conv3s2p_plan_destroy(p->s2p);
   delete p;
 }

@@ -14,6 +14,7 @@ struct yb_engine {
   std::vector<const float*> biases;
   std::vector<yb::ConvTcPlan*> plans;  // per op (nullptr unless bf16 conv)
   std::vector<yb::Conv3Plan*> plans3;  // per op (3x3 s1 slab kernel), takes precedence
+  std::vector<yb::ConvS2pPlan*> plans_s2p;  // per op (3x3 s2 pair-slab kernel for 32-channel inputs)
   cudaGraphExec_t graph_exec = nullptr;
   cudaStream_t capture_stream = nullptr;
   int launches = 0;
@@ -30,7 +31,9 @@ static int run_ops(yb_engine* e, cudaStream_t s, cudaEvent_t* evs = nullptr) {
     int rc = YB_OK;
     switch (o.kind) {
       case YB_OP_CONV: {
-        if (e->plans3[i]) {
+        if (e->plans_s2p[i]) {
+          rc = conv3s2p_launch(e->plans_s2p[i], s);
+        } else if (e->plans3[i]) {
           rc = conv3_tc_launch(e->plans3[i], s);
         } else if (e->plans[i]) {
           rc = conv_tc_launch(e->plans[i], s);
@@ -84,6 +87,7 @@ extern "C" int yb_engine_create(const yb_tensor* tensors, int n_tensors, const y
   }
   e->plans.assign(n_ops, nullptr);
   e->plans3.assign(n_ops, nullptr);
+  e->plans_s2p.assign(n_ops, nullptr);
   for (int i = 0; i < n_ops; ++i) {
     const yb_op& o = e->ops[i];
     auto ok = [&](int idx) { return idx >= -1 && idx < n_tensors; };
@@ -106,6 +110,7 @@ extern "C" int yb_engine_create(const yb_tensor* tensors, int n_tensors, const y
     d.cin_pad = o.cin_pad; d.cout_pad = o.cout_pad; d.k = o.k; d.stride = o.stride; d.act = o.act;
     d.leaky_slope = o.leaky_slope; d.upsample = o.upsample; d.tile_n = o.tile_n; d.stages = o.stages;
     int rc = d.tile_n < 0 ? YB_ERR_UNSUPPORTED : conv3_tc_plan_create(d, &e->plans3[i]);
+    if (rc == YB_ERR_UNSUPPORTED && d.tile_n >= 0) rc = conv3s2p_plan_create(d, &e->plans_s2p[i]);
     if (rc == YB_ERR_UNSUPPORTED) {
       if (d.tile_n < 0) d.tile_n = -d.tile_n == 1 ? 0 : -d.tile_n;   // negative tile_n forces the generic kernel
       rc = conv_tc_plan_create(d, &e->plans[i]);
@@ -162,6 +167,7 @@ extern "C" void yb_engine_destroy(yb_engine* e) {
   if (!e) return;
   for (auto* p : e->plans) conv_tc_plan_destroy(p);
   for (auto* p : e->plans3) conv3_tc_plan_destroy(p);
+  for (auto* p : e->plans_s2p) conv3s2p_plan_destroy(p);
   if (e->graph_exec) cudaGraphExecDestroy(e->graph_exec);
   if (e->capture_stream) cudaStreamDestroy(e->capture_stream);
   delete e;
