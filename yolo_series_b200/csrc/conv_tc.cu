@@ -189,18 +189,24 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     const int row = q * 32 + lane;
     const uint32_t xr = (uint32_t)(row & 7);
     const int nchunks = G.BN / 32;
-    // A round = every epilogue warp converts G.epi_cpr 32-column chunks (the two warps of a lane quarter take the
-    // even / odd chunks), followed by one barrier and the TMA store of the round's columns from a ring slot.
-    const int cpr = G.epi_cpr;
-    const int nrounds = (nchunks + 2 * cpr - 1) / (2 * cpr);
-    const uint32_t round_cols = 64u * (uint32_t)cpr;
-    const bool store_thread = (warp == 2 && lane == 0);
+    // Two ways to spread a tile over the eight epilogue warps:
+    //  alt (two staging slots fit): the two groups of four warps (each covers the four TMEM lane quarters) take
+    //      alternate tiles -- group g owns accumulator g and slot g -- so two tiles' tcgen05.ld -> math -> store
+    //      chains are in flight; for short-K layers that chain's latency is the critical path.
+    //  single slot: all eight warps share every tile, the two warps of a lane quarter taking the even / odd
+    //      32-column chunks.
+    const bool alt = G.epi_ring >= 2;
+    const int grp = alt ? half : 0;
+    const int nthr = alt ? 128 : 256;
+    const bool store_thread = alt ? ((ew & 3) == 0 && lane == 0) : (warp == 2 && lane == 0);
+    const uint32_t tile_stage = (G.out_f32 ? 32768u : 16384u) * (uint32_t)G.epi_cpr;
+    const uint32_t sbase = staging + (uint32_t)grp * tile_stage;
+    const int c_first = alt ? 0 : half, c_step = alt ? 1 : 2;
     // The activation is a compile-time constant inside the loop (straight-line element code).
     auto run = [&](auto act_c) {
       constexpr int ACT = decltype(act_c)::value;
-      uint32_t slot = 0;
-      int it = 0;
-      for (int t = t_first; t < t_end; t += t_step, ++it) {
+      int it = grp;
+      for (int t = t_first + grp * t_step; t < t_end; t += (alt ? 2 : 1) * t_step, it += alt ? 2 : 1) {
         const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
         const int n_tile = G.resident ? res_n : t % G.tiles_n;
         int m_tile = G.resident ? t : t / G.tiles_n;
@@ -210,57 +216,36 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
         const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
         mbar_wait(bar_tfull0 + 8u * acc, aph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // the slot's previous stores (issued a whole tile ago by this store thread) must have read it
+        if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(nthr) : "memory");
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)G.BN;
-        for (int r = 0; r < nrounds; ++r) {
-          const uint32_t sbase = staging + slot * round_bytes;
-          if (G.epi_ring == 1) {   // single slot: wait (lazily) until the previous store has read it
-            if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-            asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
-          }
-          for (int u = 0; u < cpr; ++u) {
-            const int cc = 2 * cpr * r + 2 * u + half;
-            if (cc < nchunks) {
-              uint32_t v[32];
-              tmem_ld32(taddr + (uint32_t)(cc * 32), v);
-              const float* bs = bias_s + n0 + cc * 32;
-              if (G.out_f32) epi_chunk_f32<ACT>(v, bs, G.slope, sbase + (uint32_t)(2 * u + half) * 16384u + (uint32_t)row * 128u, xr);
-              else epi_chunk_bf16<ACT>(v, bs, G.slope, sbase + (uint32_t)u * 16384u + (uint32_t)row * 128u, (uint32_t)half, xr);
-            }
-          }
-          if (r == nrounds - 1) asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to TMA
-          // Before the barrier releases the next round onto the next ring slot, its previous store must have
-          // finished reading it: that store is ring - 1 commits back, and this round's is not committed yet.
-          if (store_thread) {
-            if (G.epi_ring >= 4) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
-            else if (G.epi_ring == 3) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-            else if (G.epi_ring == 2) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-          }
-          asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
-          if (store_thread) {
-            if (r == nrounds - 1) mbar_arrive(bar_tempty0 + 8u * acc);   // every warp has read this accumulator
-            const int col0 = n0 + (int)round_cols * r;
-            for (int mp = 0; mp < G.n_store_maps; ++mp) {
-              if (G.out_f32) {   // 32-column slots
-                for (int j = 0; j < 2 * cpr; ++j)
-                  if (2 * cpr * r + j < nchunks)
-                    tma_store_4d(&G.tm_y[mp], sbase + (uint32_t)j * 16384u, col0 + 32 * j, w0, G.flat ? 0 : h0, img);
-              } else {           // 64-column slots
-                for (int u = 0; u < cpr; ++u)
-                  if (2 * cpr * r + 2 * u < nchunks)
-                    tma_store_4d(&G.tm_y[mp], sbase + (uint32_t)u * 16384u, col0 + 64 * u, w0, G.flat ? 0 : h0, img);
-              }
-            }
-            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-          }
-          slot = slot + 1 == (uint32_t)G.epi_ring ? 0u : slot + 1;
+        for (int cc = c_first; cc < nchunks; cc += c_step) {
+          uint32_t v[32];
+          tmem_ld32(taddr + (uint32_t)(cc * 32), v);
+          const float* bs = bias_s + n0 + cc * 32;
+          if (G.out_f32) epi_chunk_f32<ACT>(v, bs, G.slope, sbase + (uint32_t)cc * 16384u + (uint32_t)row * 128u, xr);
+          else epi_chunk_bf16<ACT>(v, bs, G.slope, sbase + (uint32_t)(cc >> 1) * 16384u + (uint32_t)row * 128u,
+                                   (uint32_t)(cc & 1), xr);
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to TMA
+        asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(nthr) : "memory");
+        if (store_thread) {
+          mbar_arrive(bar_tempty0 + 8u * acc);   // every warp of the tile has read this accumulator
+          const int per_group = G.out_f32 ? 32 : 64;
+          const int ngroups = (G.BN + per_group - 1) / per_group;
+          for (int mp = 0; mp < G.n_store_maps; ++mp)
+            for (int g = 0; g < ngroups; ++g)
+              tma_store_4d(&G.tm_y[mp], sbase + (uint32_t)g * 16384u, n0 + g * per_group, w0, G.flat ? 0 : h0, img);
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
       }
     };
     if (G.act == YB_ACT_SILU) run(std::integral_constant<int, YB_ACT_SILU>{});
     else if (G.act == YB_ACT_LEAKY) run(std::integral_constant<int, YB_ACT_LEAKY>{});
     else run(std::integral_constant<int, YB_ACT_NONE>{});
-    if (store_thread) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if ((ew & 3) == 0 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   __syncthreads();
   if (warp == 1) {
@@ -427,14 +412,14 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   A.epi_cpr = epi_cpr_for(A.BN, y_es);
   // A deeper ring overlaps a tile's TMA store with the next tile's epilogue math: worth its shared memory for
   // short-K layers (the epilogue is the critical path), not when it would thin out the operand pipeline.
-  int ring = 3;
+  int ring = 2;
   size_t fixed = 0;
   for (; ring >= 1; --ring) {
     fixed = tile_smem(A.BN, A.BK, y_es, A.resident != 0, total_chunks, 0, ring);
     if (ring == 1) break;
     if (fixed >= 226 * 1024) continue;
     const int st = (int)((226 * 1024 - fixed) / stage_bytes);
-    if (st >= 8 || (total_chunks <= 4 && st >= 4)) break;
+    if (st >= 8 || (total_chunks <= 6 && st >= 4)) break;
   }
   A.epi_ring = ring;
   int stages = d.stages ? d.stages : (int)((226 * 1024 - fixed) / stage_bytes);
