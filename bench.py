@@ -280,9 +280,20 @@ def main():
         all_ms = sum(r[2] for r in prof)
         flops = sum(r[3] for r in prof)
         ach = flops / (conv_ms / 1e3) / 1e12
-        line['roofline'] = {'bound': 'tensor', 'kernel': 'k_conv_tc (92 launches/step)', 'achieved': ach,
+        n_conv = sum(1 for r in prof if r[1] == 1)
+        traffic, traffic_src = None, None
+        try:   # DRAM bytes of the conv launches of one step, from the committed ncu launch list (cold-cache per launch)
+            summ = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles',
+                                               'round1_launch_summary.json')))
+            traffic = summ['conv_dram_bytes_per_step']
+            traffic_src = 'profiles/round1_launch_summary.json (ncu dram__bytes_read+write, sum over the conv launches of one step)'
+        except Exception:  # noqa: BLE001
+            pass
+        line['roofline'] = {'bound': 'tensor', 'kernel': f'tcgen05 conv kernels k_conv_tc / k_conv3_tc / k_conv3s2p_tc / k_stem_tc ({n_conv} launches/step)',
+                            'achieved': ach,
                             'peak': peaks['bf16_tflops_sustained'], 'peak_source': peak_src + ' (sustained bf16 cuBLAS)',
-                            'unit': 'TFLOP/s', 'frac': ach / peaks['bf16_tflops_sustained'], 'traffic': None,
+                            'unit': 'TFLOP/s', 'frac': ach / peaks['bf16_tflops_sustained'], 'traffic': traffic,
+                            'traffic_source': traffic_src,
                             'flops_per_step': flops, 'conv_ms_per_step': conv_ms, 'trunk_ms_per_step_eager': all_ms,
                             'conv_share_of_trunk': conv_ms / all_ms}
         top = sorted(prof, key=lambda r: -r[2])[:8]
