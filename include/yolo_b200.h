@@ -191,6 +191,38 @@ int yb_engine_profile(yb_engine* e, float* ms_per_op, void* stream);
 int yb_engine_num_launches(const yb_engine* e);
 void yb_engine_destroy(yb_engine* e);
 
+/* ------------------------------------------------------------------ pre-processing
+ * letterbox (utils/datasets.py:1277-1307) fused with the detect-side conversion (datasets.py:198-199,
+ * detect.py:100-104): bilinear resize with the arithmetic of cv2.resize(INTER_LINEAR) on uint8 (11-bit
+ * fixed-point weights; an exact 2x reduction is the 2x2 box average), constant border, optional
+ * BGR->RGB swap and HWC->CHW.  The geometry (new_w/new_h/top/left, datasets.py:1283-1304) is computed
+ * by the caller; images of one call may have different source sizes.
+ */
+typedef struct {
+  const void* src;        /* device, uint8, HWC, 3 channels */
+  int64_t src_pitch;      /* bytes between source rows */
+  int32_t src_h, src_w;
+  int32_t new_w, new_h;   /* resized size before padding (== src size: no resampling) */
+  int32_t top, left;      /* where the resized image sits in the destination */
+} yb_letterbox_src;
+
+#define YB_LAYOUT_HWC 0   /* dst (B, dst_h, dst_w, 3): what letterbox() itself returns */
+#define YB_LAYOUT_CHW 1   /* dst (B, 3, dst_h, dst_w): what the model reads (datasets.py:198) */
+
+int yb_letterbox(const yb_letterbox_src* srcs /* host array */, int B, void* dst, int dst_h, int dst_w,
+                 int layout, int swap_rb, const uint8_t border[3] /* in source channel order */,
+                 void* stream);
+
+/* ------------------------------------------------------------------ post-NMS rescale
+ * scale_coords + clip_coords (utils/general.py:340-361) and, if do_round, the .round() of detect.py:183
+ * on detection rows [x1,y1,x2,y2,...] of `row_stride` floats, in place, fp32:
+ *   x = clamp((x - pad_x) / gain, 0, w0), y = clamp((y - pad_y) / gain, 0, h0)   (true division).
+ * table (device): per image [gain, pad_x, pad_y, w0, h0].  counts (device, nullable): rows of image b that
+ * are valid (NMS `counts`); NULL = all max_rows rows.
+ */
+int yb_scale_coords(float* dets, int B, int max_rows, int row_stride, const int32_t* counts,
+                    const float* table, int do_round, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

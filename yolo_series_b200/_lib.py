@@ -20,7 +20,7 @@ EXPORTS = [
     'yb_conv_plan_destroy', 'yb_maxpool2x2', 'yb_maxpool_s1', 'yb_spp3',
     'yb_upsample2x', 'yb_copy', 'yb_add', 'yb_stage_input', 'yb_stem_conv', 'yb_decode', 'yb_nms_workspace_bytes',
     'yb_nms', 'yb_decode_nms', 'yb_engine_create', 'yb_engine_forward', 'yb_engine_num_launches', 'yb_engine_profile',
-    'yb_engine_destroy',
+    'yb_engine_destroy', 'yb_letterbox', 'yb_scale_coords',
 ]
 
 
@@ -46,6 +46,13 @@ class Op(C.Structure):
                 ('act', C.c_int32), ('upsample', C.c_int32), ('leaky_slope', C.c_float), ('weight', C.c_int32),
                 ('cin_pad', C.c_int32), ('cout_pad', C.c_int32), ('tile_n', C.c_int32), ('stages', C.c_int32)]
 
+
+class LetterboxSrc(C.Structure):
+    _fields_ = [('src', C.c_void_p), ('src_pitch', C.c_int64), ('src_h', C.c_int32), ('src_w', C.c_int32),
+                ('new_w', C.c_int32), ('new_h', C.c_int32), ('top', C.c_int32), ('left', C.c_int32)]
+
+
+LAYOUT_HWC, LAYOUT_CHW = 0, 1
 
 _lib = None
 
@@ -91,6 +98,9 @@ def lib():
                                 C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.yb_engine_create.argtypes = [C.POINTER(Tensor), C.c_int, C.POINTER(Op), C.c_int, C.POINTER(C.c_void_p),
                                    C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_void_p)]
+    L.yb_letterbox.argtypes = [C.POINTER(LetterboxSrc), C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                               C.POINTER(C.c_uint8), C.c_void_p]
+    L.yb_scale_coords.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     if L.yb_abi_version() != 1:
         raise RuntimeError('libyolo_b200.so ABI version mismatch; rebuild')
     _lib = L
