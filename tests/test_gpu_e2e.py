@@ -111,3 +111,26 @@ def test_batch_consistency_and_oracle_b2():
     o, _ = ref_forward(zoo.get_cfg('yolov7-tiny'), sd, x, fused=True)
     assert float((p2[..., :4] - o[..., :4]).abs().max()) <= 1e-2
     assert float((p2[..., 4:] - o[..., 4:]).abs().max()) <= 1e-3
+
+
+def test_detect_batches_stream_equals_detect():
+    """The three-stream pipeline (Model.detect_batches) returns, batch by batch and in order, exactly what the
+    blocking Model.detect returns; ragged last batch and a dtype change rebuild the slot buffers."""
+    m = _build('yolov7-tiny', 'bf16')
+    batches = [synth_image(b, 96, 128, seed=20 + i, dtype=torch.uint8).pin_memory()
+               for i, b in enumerate([4, 4, 4, 4, 4, 2])]
+    want = []
+    for xb in batches:
+        out, meta = m.detect(xb, 0.05, 0.5, max_det=50, packed=True)
+        want.append((out.cpu(), meta[:-1].cpu()))
+    got = []
+    for out, cnt in m.detect_batches(iter(batches), 0.05, 0.5, max_det=50):
+        assert out.is_pinned() and out.device.type == 'cpu'
+        got.append((out.clone(), cnt.clone()))
+    assert len(got) == len(want)
+    for (o, c), (wo, wc) in zip(got, want):
+        assert torch.equal(c, wc)
+        for i in range(o.shape[0]):
+            assert torch.equal(o[i, :c[i]], wo[i, :c[i]])
+    assert sum(int(c.sum()) for _, c in got) > 0
+    assert list(m.detect_batches(iter([]), 0.05, 0.5)) == []

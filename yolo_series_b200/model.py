@@ -232,6 +232,9 @@ class Model(nn.Module):
 
     def head_levels(self, eng):
         head = self._layers()[-1]
+        cached = getattr(eng, '_head_lv', None)    # anchors are read back once per engine: .cpu() would drain the stream
+        if cached is not None:
+            return cached, head
         lv = (_lib.HeadLevel * head.nl)()
         ag = head.anchor_grid.detach().float().cpu().view(head.nl, -1, 2)
         for i in range(head.nl):
@@ -240,6 +243,7 @@ class Model(nn.Module):
             for a in range(head.na):
                 lv[i].anchor_wh[2 * a] = float(ag[i, a, 0])
                 lv[i].anchor_wh[2 * a + 1] = float(ag[i, a, 1])
+        eng._head_lv = lv
         return lv, head
 
     def run_trunk(self, x):
@@ -288,6 +292,72 @@ class Model(nn.Module):
         A = sum(head.na * v.H * v.W for v in eng.head_views)
         return _run_nms(None, eng.B, A, head.no, conf_thres, iou_thres, classes, agnostic, multi_label, max_nms,
                         max_det, eng.device, levels=(lv, head.nl, head.na), return_packed=packed)
+
+
+    @torch.no_grad()
+    def detect_batches(self, batches, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False,
+                       multi_label=False, max_det=300, max_nms=30000, post=None):
+        """Streaming form of ``detect`` for host batches (the detect.py:87-152 loop over a dataset): a generator that
+        takes (B, 3, H, W) uint8/float32 HOST tensors (pinned for real overlap) and yields, in order, one
+        ``(out (B', max_det, 6) fp32, counts (B',) int32)`` pair of pinned HOST tensors per batch.
+
+        Three streams, two slots: batch i+1's H2D copy and batch i-1's D2H read run on their own copy streams
+        while batch i computes on the caller's stream, so PCIe time leaves the critical path; each step still
+        moves its own input H2D and its own result D2H.  ``post(out, counts) -> (out, counts)`` runs on the compute
+        stream before the read-back (e.g. ``dist.gather_detections``).  A yielded pair stays valid until the next
+        batch is drawn (its pinned buffers are reused two batches later)."""
+        from collections import deque
+        dev = self._device()
+        if dev.type != 'cuda':
+            raise RuntimeError('yolo_series_b200.Model needs a CUDA device (no CPU fallback)')
+        main = torch.cuda.current_stream(dev)
+        h2d, d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        slots = [dict(stage=None, host=None, consumed=torch.cuda.Event(), loaded=torch.cuda.Event(),
+                      done=torch.cuda.Event(), read=torch.cuda.Event(), used=False) for _ in range(2)]
+        pending = deque()
+
+        def finish(s):
+            s['read'].synchronize()
+            meta = s['host'][1]
+            B = meta.numel() - 1
+            if int(meta[B]) != 0:
+                raise RuntimeError('yb_nms: candidate capacity exceeded (YB_ERR_OVERFLOW)')
+            s['keep'] = None
+            return s['host'][0], meta[:B]
+
+        for i, xb in enumerate(batches):
+            s = slots[i & 1]
+            if len(pending) == 2:
+                yield finish(pending.popleft())
+            if s['stage'] is None or s['stage'].shape != xb.shape or s['stage'].dtype != xb.dtype:
+                s['stage'] = torch.empty(xb.shape, dtype=xb.dtype, device=dev)
+            if s['used']:
+                h2d.wait_event(s['consumed'])
+            with torch.cuda.stream(h2d):
+                s['stage'].copy_(xb, non_blocking=True)
+                s['loaded'].record(h2d)
+            main.wait_event(s['loaded'])
+            out, meta = self.detect(s['stage'], conf_thres, iou_thres, classes, agnostic, multi_label, max_det,
+                                    max_nms, packed=True)
+            s['consumed'].record(main)
+            ovf = meta[-1:]
+            if post is not None:
+                out, cnt = post(out, meta[:-1])
+                meta = torch.cat((cnt.to(torch.int32), ovf))
+            s['done'].record(main)
+            if s['host'] is None or s['host'][0].shape != out.shape:
+                s['host'] = (torch.empty(out.shape, dtype=out.dtype).pin_memory(),
+                             torch.empty(meta.shape, dtype=meta.dtype).pin_memory())
+            d2h.wait_event(s['done'])
+            with torch.cuda.stream(d2h):
+                s['host'][0].copy_(out, non_blocking=True)
+                s['host'][1].copy_(meta, non_blocking=True)
+                s['read'].record(d2h)
+            s['keep'] = (out, meta)          # device results stay referenced until the read-back has completed
+            s['used'] = True
+            pending.append(s)
+        while pending:
+            yield finish(pending.popleft())
 
 
 class AcceleratedModel(Model):
