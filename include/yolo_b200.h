@@ -223,6 +223,52 @@ int yb_letterbox(const yb_letterbox_src* srcs /* host array */, int B, void* dst
 int yb_scale_coords(float* dets, int B, int max_rows, int row_stride, const int32_t* counts,
                     const float* table, int do_round, void* stream);
 
+/* ------------------------------------------------------------------ TTA / ensemble
+ * Model.forward(augment=True) (models/yolo.py:582-597) runs the forward at scales 1 / 0.83 / 0.67 (the 0.83 pass
+ * left-right flipped), de-scales / de-flips each pass's boxes and concatenates the passes along dim 1;
+ * Ensemble.forward (models/experimental.py:74-81) concatenates the outputs of several models the same way.
+ *
+ * yb_scale_img: scale_img (utils/torch_utils.py:247-257) fused with the flip of yolo.py:588:
+ *   dst (B, C, dst_h, dst_w) fp32 = F.pad(F.interpolate(flip(src), size=(h, w), mode='bilinear',
+ *   align_corners=False), [0, dst_w - w, 0, dst_h - h], value=pad_value);  src (B, C, H, W) fp32, or uint8
+ *   (scaled by 1/255 first, detect.py:103).  flip: 0 none, 2 up-down, 3 left-right (the reference's dim numbers).
+ *   Bit-identical to ATen's CPU bilinear kernel (torch 2.11) on fp32 input.
+ * yb_decode_tta: yb_decode of one pass into rows [row_off, row_off + A_pass) of pred (B, rows_total, no) with
+ *   xywh /= scale; flip 2: y = img_h - y; flip 3: x = img_w - x   (yolo.py:591-595).  No raw output (the
+ *   reference returns None for it).
+ */
+typedef struct {
+  int32_t rows_total; /* rows per image of the destination pred (sum over all passes / ensemble members) */
+  int32_t row_off;    /* first destination row of this pass */
+  float scale;        /* de-scale divisor si; 1 = none */
+  int32_t flip;       /* 0, 2 or 3 */
+  float img_h, img_w; /* size of the un-augmented input (yolo.py:583) */
+} yb_tta_pass;
+
+int yb_scale_img(const void* src, int src_dtype, int B, int C, int H, int W, int flip, int h, int w, float* dst,
+                 int dst_h, int dst_w, float pad_value, void* stream);
+int yb_decode_tta(const yb_head_level* levels, int nl, int na, int no, float* pred, const yb_tta_pass* pass,
+                  void* stream);
+
+/* ------------------------------------------------------------------ evaluation matching
+ * yb_box_iou: box_iou (utils/general.py:464-486): iou (n, m) fp32 of xyxy boxes, rows of stride1 / stride2 floats.
+ * yb_match_detections: the per-image statistics of test.py:179-210 for a whole batch in one launch.
+ *   dets (B, max_det, 6) + counts (B, nullable): NMS output in inference space (not modified).
+ *   targets (T, 6) fp32 rows [image, class, x, y, w, h], pixels in inference space (test.py:109), grouped by image
+ *   in ascending order (what collate_fn produces, utils/datasets.py:621-626).
+ *   table (B, 5): per image [gain, pad_x, pad_y, w0, h0] of scale_coords (test.py:144,190; general.py:340-361).
+ *   iouv (niou): IoU thresholds (test.py:92: linspace(0.5, 0.95, 10)).
+ *   correct (B, max_det, niou) uint8 0/1 = the reference's `correct` per image (rows >= counts[b] are 0).
+ *   detected (T, nullable) uint8: which targets were claimed.
+ *   status (device int, caller-zeroed): bit 0 = targets not grouped by image / index out of range.
+ * Bit-identical to the reference (fp32 IoU, first-maximum ties, greedy claim in confidence order).
+ */
+int yb_box_iou(const float* box1, int n, int stride1, const float* box2, int m, int stride2, float* iou,
+               void* stream);
+int yb_match_detections(const float* dets, const int32_t* counts, int B, int max_det, const float* targets, int T,
+                        const float* table, const float* iouv, int niou, uint8_t* correct, uint8_t* detected,
+                        int* status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

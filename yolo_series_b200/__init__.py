@@ -6,8 +6,8 @@ not a legal Python identifier).  All compute lives in ``libyolo_b200.so`` (csrc/
 include/yolo_b200.h); importing the package does not load it, calling any operator does and raises
 if it is missing -- there is no CPU fallback.
 """
-from .model import Model, accelerate, parse_model          # noqa: F401
+from .model import Ensemble, Model, accelerate, parse_model  # noqa: F401
 from .nms import non_max_suppression                        # noqa: F401
 from .zoo import get_cfg                                    # noqa: F401
 
-__all__ = ['Model', 'accelerate', 'parse_model', 'non_max_suppression', 'get_cfg']
+__all__ = ['Model', 'Ensemble', 'accelerate', 'parse_model', 'non_max_suppression', 'get_cfg']

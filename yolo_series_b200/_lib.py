@@ -20,7 +20,8 @@ EXPORTS = [
     'yb_conv_plan_destroy', 'yb_maxpool2x2', 'yb_maxpool_s1', 'yb_spp3',
     'yb_upsample2x', 'yb_copy', 'yb_add', 'yb_stage_input', 'yb_stem_conv', 'yb_decode', 'yb_nms_workspace_bytes',
     'yb_nms', 'yb_decode_nms', 'yb_engine_create', 'yb_engine_forward', 'yb_engine_num_launches', 'yb_engine_profile',
-    'yb_engine_destroy', 'yb_letterbox', 'yb_scale_coords',
+    'yb_engine_destroy', 'yb_letterbox', 'yb_scale_coords', 'yb_scale_img', 'yb_decode_tta', 'yb_box_iou',
+    'yb_match_detections',
 ]
 
 
@@ -50,6 +51,11 @@ class Op(C.Structure):
 class LetterboxSrc(C.Structure):
     _fields_ = [('src', C.c_void_p), ('src_pitch', C.c_int64), ('src_h', C.c_int32), ('src_w', C.c_int32),
                 ('new_w', C.c_int32), ('new_h', C.c_int32), ('top', C.c_int32), ('left', C.c_int32)]
+
+
+class TtaPass(C.Structure):
+    _fields_ = [('rows_total', C.c_int32), ('row_off', C.c_int32), ('scale', C.c_float), ('flip', C.c_int32),
+                ('img_h', C.c_float), ('img_w', C.c_float)]
 
 
 LAYOUT_HWC, LAYOUT_CHW = 0, 1
@@ -101,6 +107,13 @@ def lib():
     L.yb_letterbox.argtypes = [C.POINTER(LetterboxSrc), C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
                                C.POINTER(C.c_uint8), C.c_void_p]
     L.yb_scale_coords.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+    L.yb_scale_img.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                               C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p]
+    L.yb_decode_tta.argtypes = [C.POINTER(HeadLevel), C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(TtaPass),
+                                C.c_void_p]
+    L.yb_box_iou.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    L.yb_match_detections.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                      C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     if L.yb_abi_version() != 1:
         raise RuntimeError('libyolo_b200.so ABI version mismatch; rebuild')
     _lib = L

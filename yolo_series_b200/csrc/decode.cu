@@ -28,6 +28,9 @@ struct DecodeLevel {
   float anchor_wh[2 * YB_MAX_ANCHORS];
   int row_off;  // first pred row of this level within an image
   float* raw;   // nullable
+  // TTA pass (yolo.py:591-595): xywh /= scale, then y = img_h - y (flip 2) or x = img_w - x (flip 3)
+  float scale, img_h, img_w;
+  int flip;
 };
 
 template <typename T>
@@ -45,6 +48,11 @@ __global__ void __launch_bounds__(256) k_decode(DecodeLevel L, int B, int A, int
     float t = Elem<T>::load(in + p * L.c_stride + c);
     int a = c / no, o = c - a * no;
     float v = decode_elem(sigmoid_rn(t), o, x, y, L.stride, L.anchor_wh[2 * a], L.anchor_wh[2 * a + 1]);
+    if (o < 4) {
+      if (L.scale != 1.0f) v = __fdiv_rn(v, L.scale);
+      if (o == 1 && L.flip == 2) v = __fsub_rn(L.img_h, v);
+      if (o == 0 && L.flip == 3) v = __fsub_rn(L.img_w, v);
+    }
     size_t cell = ((size_t)a * L.ny + y) * L.nx + x;
     pred[((size_t)b * A + L.row_off + cell) * no + o] = v;
     if (L.raw) L.raw[(((size_t)b * na) * L.ny * L.nx + cell) * no + o] = t;
@@ -55,8 +63,8 @@ __global__ void __launch_bounds__(256) k_decode(DecodeLevel L, int B, int A, int
 
 using namespace yb;
 
-extern "C" int yb_decode(const yb_head_level* levels, int nl, int na, int no, float* pred, float* const* raw,
-                         void* stream) {
+static int decode_impl(const yb_head_level* levels, int nl, int na, int no, float* pred, float* const* raw,
+                       const yb_tta_pass* pass, void* stream) {
   YB_CHECK_ARG(levels && pred && nl > 0 && nl <= YB_MAX_LEVELS, "yb_decode: bad levels");
   YB_CHECK_ARG(na > 0 && na <= YB_MAX_ANCHORS && no > 5 - 1, "yb_decode: bad na/no");
   int A = 0;
@@ -67,7 +75,14 @@ extern "C" int yb_decode(const yb_head_level* levels, int nl, int na, int no, fl
     YB_CHECK_ARG(t.dtype == YB_F32 || t.dtype == YB_BF16, "yb_decode: logits must be fp32/bf16");
     A += na * t.H * t.W;
   }
-  int off = 0;
+  int off = 0, rows = A;
+  if (pass) {
+    YB_CHECK_ARG(pass->row_off >= 0 && pass->rows_total >= pass->row_off + A, "yb_decode_tta: rows [%d, %d) exceed %d",
+                 pass->row_off, pass->row_off + A, pass->rows_total);
+    YB_CHECK_ARG(pass->scale > 0.0f && (pass->flip == 0 || pass->flip == 2 || pass->flip == 3), "yb_decode_tta: bad scale/flip");
+    off = pass->row_off;
+    rows = pass->rows_total;
+  }
   for (int l = 0; l < nl; ++l) {
     const yb_tensor& t = levels[l].logits;
     DecodeLevel L;
@@ -76,13 +91,28 @@ extern "C" int yb_decode(const yb_head_level* levels, int nl, int na, int no, fl
     memcpy(L.anchor_wh, levels[l].anchor_wh, sizeof(L.anchor_wh));
     L.row_off = off;
     L.raw = raw ? raw[l] : nullptr;
+    L.scale = pass ? pass->scale : 1.0f;
+    L.flip = pass ? pass->flip : 0;
+    L.img_h = pass ? pass->img_h : 0.0f;
+    L.img_w = pass ? pass->img_w : 0.0f;
     size_t total = (size_t)B * t.H * t.W * na * no;
     size_t g = (total + 255) / 256, cap = (size_t)num_sms() * 16;
     int grid = (int)(g < cap ? g : cap);
-    if (t.dtype == YB_F32) k_decode<float><<<grid, 256, 0, (cudaStream_t)stream>>>(L, B, A, na, no, pred);
-    else k_decode<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(L, B, A, na, no, pred);
+    if (t.dtype == YB_F32) k_decode<float><<<grid, 256, 0, (cudaStream_t)stream>>>(L, B, rows, na, no, pred);
+    else k_decode<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(L, B, rows, na, no, pred);
     YB_LAUNCH_CHECK();
     off += na * t.H * t.W;
   }
   return YB_OK;
+}
+
+extern "C" int yb_decode(const yb_head_level* levels, int nl, int na, int no, float* pred, float* const* raw,
+                         void* stream) {
+  return decode_impl(levels, nl, na, no, pred, raw, nullptr, stream);
+}
+
+extern "C" int yb_decode_tta(const yb_head_level* levels, int nl, int na, int no, float* pred, const yb_tta_pass* pass,
+                             void* stream) {
+  YB_CHECK_ARG(pass, "yb_decode_tta: pass is NULL");
+  return decode_impl(levels, nl, na, no, pred, nullptr, pass, stream);
 }

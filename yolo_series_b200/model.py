@@ -265,10 +265,73 @@ class Model(nn.Module):
         eng.run()
         return eng
 
+    # ---- TTA / ensemble plumbing (yolo.py:582-597, experimental.py:74-81)
+    TTA_SCALES = (1, 0.83, 0.67)
+    TTA_FLIPS = (None, 3, None)      # 2 = up-down, 3 = left-right
+
+    def _passes(self, H, W, augment):
+        """[(scale, flip, (h, w) resized, (Hp, Wp) padded)] of one call (scale_img, torch_utils.py:247-257)."""
+        if not augment:
+            return [(1, None, (H, W), (H, W))]
+        gs = int(self.stride.max())
+        out = []
+        for si, fi in zip(self.TTA_SCALES, self.TTA_FLIPS):
+            if si == 1.0:
+                out.append((si, fi, (H, W), (H, W)))
+            else:
+                out.append((si, fi, (int(H * si), int(W * si)),
+                            (math.ceil(H * si / gs) * gs, math.ceil(W * si / gs) * gs)))
+        return out
+
+    def rows_per_image(self, H, W, augment=False):
+        """A of ``pred`` for an (H, W) input: na * sum of the level grids, summed over the TTA passes."""
+        head = self._layers()[-1]
+        strides = [int(s) for s in head.stride.tolist()]
+        return sum(head.na * sum((hp // s) * (wp // s) for s in strides) for _, _, _, (hp, wp) in self._passes(H, W, augment))
+
+    def _scaled_input(self, x, si, fi, hw, HW):
+        """scale_img(x.flip(fi), si) as one kernel (yb_scale_img): fp32 (B, C, Hp, Wp) on the device."""
+        dev = x.device if x.device.type == 'cuda' else self._device()
+        if x.device != dev:
+            x = x.to(dev, non_blocking=True)
+        x = x.contiguous()
+        B, Cc, H, W = x.shape
+        out = torch.empty((B, Cc, HW[0], HW[1]), dtype=torch.float32, device=dev)
+        code = _lib.YB_U8 if x.dtype == torch.uint8 else _lib.YB_F32
+        _lib.check(_lib.lib().yb_scale_img(C.c_void_p(x.data_ptr()), code, B, Cc, H, W, int(fi or 0), hw[0], hw[1],
+                                           C.c_void_p(out.data_ptr()), HW[0], HW[1], 0.447, _lib.stream_ptr()),
+                   'yb_scale_img')
+        return out
+
+    def forward_into(self, x, pred, row_off, augment=False):
+        """Decode this model's prediction rows for ``x`` into ``pred[:, row_off:row_off + rows]`` (B, rows_total, no)
+        and return the number of rows written.  Used by ``forward(augment=True)`` and ``Ensemble`` so the
+        ``torch.cat(y, 1)`` of yolo.py:597 / experimental.py:80 never happens as a copy."""
+        if x.dtype not in (torch.uint8, torch.float32):
+            x = x.float()
+        B, _, H, W = x.shape
+        written = 0
+        for si, fi, hw, HW in self._passes(H, W, augment):
+            xi = x if (si == 1.0 and not fi) else self._scaled_input(x, si, fi, hw, HW)
+            eng = self.run_trunk(xi)
+            lv, head = self.head_levels(eng)
+            A = sum(head.na * v.H * v.W for v in eng.head_views)
+            tp = _lib.TtaPass(pred.shape[1], row_off + written, float(si), int(fi or 0), float(H), float(W))
+            _lib.check(eng.lib.yb_decode_tta(lv, head.nl, head.na, head.no, C.c_void_p(pred.data_ptr()), C.byref(tp),
+                                             _lib.stream_ptr()), 'yb_decode_tta')
+            written += A
+        return written
+
     @torch.no_grad()
     def forward(self, x, augment=False, profile=False):
         if augment:
-            raise NotImplementedError('TTA (yolo.py:582-597) is a "next" row (SURVEY.md 8f), not built yet')
+            # augmented inference (yolo.py:582-597): three passes decoded straight into one pred, de-scaled / de-flipped
+            B, _, H, W = x.shape
+            head = self._layers()[-1]
+            dev = x.device if x.device.type == 'cuda' else self._device()
+            pred = torch.empty((B, self.rows_per_image(H, W, True), head.no), dtype=torch.float32, device=dev)
+            self.forward_into(x, pred, 0, augment=True)
+            return pred, None
         eng = self.run_trunk(x)
         lv, head = self.head_levels(eng)
         A = sum(head.na * v.H * v.W for v in eng.head_views)
@@ -282,11 +345,15 @@ class Model(nn.Module):
 
     @torch.no_grad()
     def detect(self, x, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False, multi_label=False,
-               max_det=300, max_nms=30000, packed=False):
+               max_det=300, max_nms=30000, packed=False, augment=False):
         """Fused fast path: forward + decode + NMS without materialising ``pred`` (yb_decode_nms).
         Returns the same list as ``non_max_suppression(model(x)[0], ...)``; ``packed=True`` returns the device
         buffers ``(out (B,max_det,6), meta int32 [counts..., overflow])`` with no host synchronisation."""
         from .nms import _run_nms
+        if augment:      # TTA: the passes share one pred, then the stand-alone NMS (3x the candidates)
+            pred = self.forward(x, augment=True)[0]
+            return _run_nms(pred, pred.shape[0], pred.shape[1], pred.shape[2], conf_thres, iou_thres, classes, agnostic,
+                            multi_label, max_nms, max_det, pred.device, return_packed=packed)
         eng = self.run_trunk(x)
         lv, head = self.head_levels(eng)
         A = sum(head.na * v.H * v.W for v in eng.head_views)
@@ -385,3 +452,36 @@ class AcceleratedModel(Model):
 def accelerate(ref_model):
     """Return a drop-in module whose forward runs on the B200 engine using ``ref_model``'s weights."""
     return AcceleratedModel(ref_model)
+
+
+class Ensemble(nn.ModuleList):
+    """Drop-in for models/experimental.py:68-81: NMS ensemble = the members' predictions concatenated along dim 1.
+    Every member decodes straight into its row range of one ``pred`` buffer (no ``torch.cat`` copy)."""
+
+    def __init__(self, models=()):
+        super().__init__(models)
+
+    @torch.no_grad()
+    def forward(self, x, augment=False):
+        if not len(self):
+            raise RuntimeError('Ensemble is empty')
+        B, _, H, W = x.shape
+        rows = [m.rows_per_image(H, W, augment) for m in self]
+        no = self[0]._layers()[-1].no
+        if any(m._layers()[-1].no != no for m in self):
+            raise ValueError('Ensemble members must share nc (torch.cat along dim 1, experimental.py:80)')
+        dev = x.device if x.device.type == 'cuda' else self[0]._device()
+        pred = torch.empty((B, sum(rows), no), dtype=torch.float32, device=dev)
+        off = 0
+        for m, r in zip(self, rows):
+            assert m.forward_into(x, pred, off, augment) == r
+            off += r
+        return pred, None
+
+    @property
+    def stride(self):
+        return self[-1].stride
+
+    @property
+    def names(self):
+        return self[-1].names
