@@ -21,7 +21,7 @@ from yolo_series_b200.preprocess import letterbox_batch, rescale_detections  # n
 
 PEAK = 6545.6
 try:
-    PEAK = float(json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['hbm_copy_GBps'])
+    PEAK = float(json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['hbm_gbs'])
 except Exception:
     pass
 

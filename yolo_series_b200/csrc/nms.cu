@@ -255,15 +255,15 @@ __global__ void __launch_bounds__(kFbThreads) k_filter_best(const FilterParams P
   extern __shared__ __align__(16) unsigned char fb_smem[];
   float* tile = reinterpret_cast<float*>(fb_smem);             // [kFbThreads][pitch]
   __shared__ uint64_t kbuf[kFbThreads];
-  __shared__ int s_n, s_base;
+  __shared__ int s_n, s_cnt, s_base;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int pitch = P.no | 1;
   const int b = blockIdx.x / P.blocks_per_img, blk = blockIdx.x - b * P.blocks_per_img;
   const int row_begin = blk * P.rows_per_block;
   const int row_end = min(P.A, row_begin + P.rows_per_block);
+  if (tid == 0) s_n = 0;       // re-armed by thread 0 after every flush (never while another thread may read it)
   for (int t0 = row_begin; t0 < row_end; t0 += kFbThreads) {
     const int t1 = min(row_end, t0 + kFbThreads);
-    if (tid == 0) s_n = 0;
     // ---- stage rows [t0, t1): warp w owns rows t0 + w + 4k; eight rows' loads are issued before their stores
     constexpr int kWarpsFb = kFbThreads / 32;
     for (int row0 = t0 + warp; row0 < t1; row0 += kFbInflight * kWarpsFb) {
@@ -335,14 +335,134 @@ __global__ void __launch_bounds__(kFbThreads) k_filter_best(const FilterParams P
     pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mk & ((1u << lane) - 1u));
     if (emit) kbuf[pos] = key;
     __syncthreads();
-    if (tid == 0) s_base = s_n ? atomicAdd(P.count + b, s_n) : 0;
+    if (tid == 0) {
+      s_cnt = s_n;
+      s_base = s_cnt ? atomicAdd(P.count + b, s_cnt) : 0;
+      s_n = 0;
+    }
     __syncthreads();
-    if (tid < s_n) {
+    if (tid < s_cnt) {
       const int slot = s_base + tid;
       if (slot < P.cap) P.keys[(size_t)b * P.cap + slot] = kbuf[tid];
       else if (P.overflow) *P.overflow = 1;
     }
     __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_filter_bulk: best-class filter over decoded predictions (the stand-alone yb_nms, e.g. the 100 000-row stress
+// config) as a bulk-copy pipeline.  (B, A, no) fp32 is dense, so a tile of kBkRows rows is ONE contiguous span of
+// kBkRows*no*4 bytes: thread 0 streams tiles into an S-stage shared-memory ring with cp.async.bulk (completion on
+// an mbarrier per stage), S-1 tiles are always in flight per SM while the 256 threads walk one row each of the
+// current tile (dense pitch `no` must be odd -> conflict-free).  The class scan keeps four independent running
+// maxima (classes c mod 4) merged by (larger conf, then smaller index) = the first index of the maximum.
+// Needs pred 16-byte aligned, A*no % 4 == 0 (every tile start / size is then a multiple of 16 bytes) and odd no;
+// anything else takes k_filter_best.
+// ------------------------------------------------------------------------------------------------
+constexpr int kBkRows = 256;
+
+__device__ __forceinline__ uint32_t nms_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bk_mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n.reg .pred p;\nWAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bk_issue(uint32_t bar, uint32_t dst, const void* src, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+__global__ void __launch_bounds__(kBkRows) k_filter_bulk(const FilterParams P, int stages, int tile_floats) {
+  extern __shared__ __align__(128) unsigned char bk_smem[];
+  float* ring = reinterpret_cast<float*>(bk_smem);             // [stages][tile_floats]
+  __shared__ __align__(8) uint64_t full[8];
+  __shared__ uint64_t kbuf[kBkRows];
+  __shared__ int s_n, s_cnt, s_base;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int b = blockIdx.x / P.blocks_per_img, blk = blockIdx.x - b * P.blocks_per_img;
+  const int row_begin = blk * P.rows_per_block;
+  const int row_end = min(P.A, row_begin + P.rows_per_block);
+  const int ntiles = (row_end - row_begin + kBkRows - 1) / kBkRows;
+  const float* img = P.pred + (size_t)b * P.A * P.no;
+  if (tid == 0) {
+    for (int i = 0; i < stages; ++i)
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(nms_smem_u32(&full[i])));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    s_n = 0;
+    for (int i = 0; i < stages && i < ntiles; ++i) {
+      const int t0 = row_begin + i * kBkRows, rows = min(kBkRows, row_end - t0);
+      bk_issue(nms_smem_u32(&full[i]), nms_smem_u32(ring + (size_t)i * tile_floats), img + (size_t)t0 * P.no,
+               (uint32_t)rows * P.no * 4u);
+    }
+  }
+  __syncthreads();
+  const int nc = P.nc, no = P.no;
+  for (int i = 0; i < ntiles; ++i) {
+    const int st = i % stages;
+    const int t0 = row_begin + i * kBkRows, t1 = min(row_end, t0 + kBkRows);
+    bk_mbar_wait(nms_smem_u32(&full[st]), (uint32_t)(i / stages) & 1u);
+    const int row = t0 + tid;
+    bool emit = false;
+    unsigned long long key = 0ull;
+    if (row < t1) {
+      const float* r = ring + (size_t)st * tile_floats + (size_t)tid * no;
+      const float obj = r[4];
+      if (obj > P.conf_thres) {                 // general.py:637,653
+        float bv[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        int bi[4] = {0, 1, 2, 3};
+        const float* cl = r + 5;
+        int c = 0;
+        for (; c + 4 <= nc; c += 4) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const float conf = __fmul_rn(cl[c + u], obj);   // general.py:673
+            if (conf > bv[u]) { bv[u] = conf; bi[u] = c + u; }
+          }
+        }
+        for (int u = 0; c + u < nc; ++u) {
+          const float conf = __fmul_rn(cl[c + u], obj);
+          if (conf > bv[u]) { bv[u] = conf; bi[u] = c + u; }
+        }
+        float best = bv[0];
+        int best_c = bi[0];
+#pragma unroll
+        for (int u = 1; u < 4; ++u) {
+          if (bv[u] > best || (bv[u] == best && bi[u] < best_c)) { best = bv[u]; best_c = bi[u]; }
+        }
+        if (best == -INFINITY) best_c = 0;      // no class beat -inf (all NaN): argmax of the reference's scan = 0
+        if (best > P.conf_thres && class_allowed(P, best_c)) {   // general.py:684,688
+          emit = true;
+          key = ((unsigned long long)(~__float_as_uint(best)) << 32) | (uint32_t)row;
+          P.cls_of_row[(size_t)b * P.A + row] = (uint16_t)best_c;
+        }
+      }
+    }
+    __syncthreads();                              // every thread is done reading stage st
+    if (tid == 0 && i + stages < ntiles) {
+      const int n0 = row_begin + (i + stages) * kBkRows, rows = min(kBkRows, row_end - n0);
+      bk_issue(nms_smem_u32(&full[st]), nms_smem_u32(ring + (size_t)st * tile_floats), img + (size_t)n0 * no,
+               (uint32_t)rows * no * 4u);
+    }
+    const unsigned mk = __ballot_sync(0xffffffffu, emit);
+    int pos = 0;
+    if (lane == 0 && mk) pos = atomicAdd(&s_n, __popc(mk));
+    pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mk & ((1u << lane) - 1u));
+    if (emit) kbuf[pos] = key;
+    __syncthreads();
+    if (tid == 0) {                               // s_n is re-armed here: nobody touches it until the next ballot
+      s_cnt = s_n;
+      s_base = s_cnt ? atomicAdd(P.count + b, s_cnt) : 0;
+      s_n = 0;
+    }
+    __syncthreads();
+    if (tid < s_cnt) {
+      const int slot = s_base + tid;
+      if (slot < P.cap) P.keys[(size_t)b * P.cap + slot] = kbuf[tid];
+      else if (P.overflow) *P.overflow = 1;
+    }
   }
 }
 
@@ -917,6 +1037,22 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
         YB_CUDA(cudaFuncSetAttribute(k_filter_cells<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cells_smem));
         k_filter_cells<__nv_bfloat16><<<grid3, kFbThreads, cells_smem, s>>>(F);
       }
+    } else if (!fused && !F.multi_label && F.nc > 1 && (F.no & 1) && ((long long)A * F.no) % 4 == 0 &&
+               (uintptr_t)F.pred % 16 == 0 && (size_t)kBkRows * F.no * 4 * 2 <= 200 * 1024 &&
+               getenv("YB_NMS_NO_BULK") == nullptr) {
+      // decoded predictions, best class: bulk-copy ring (k_filter_bulk)
+      const int tile_floats = kBkRows * F.no;
+      int stages = (int)((200 * 1024) / ((size_t)tile_floats * 4));
+      if (stages > 4) stages = 4;
+      const int tiles_img = (A + kBkRows - 1) / kBkRows;
+      int bpi3 = (num_sms() * 8 + B - 1) / B;                 // ~8 blocks per SM over the batch
+      if (bpi3 > (tiles_img + 1) / 2) bpi3 = (tiles_img + 1) / 2;   // at least two tiles per block
+      if (bpi3 < 1) bpi3 = 1;
+      F.rows_per_block = ((tiles_img + bpi3 - 1) / bpi3) * kBkRows;
+      F.blocks_per_img = (A + F.rows_per_block - 1) / F.rows_per_block;
+      const size_t bk_bytes = (size_t)stages * tile_floats * 4;
+      YB_CUDA(cudaFuncSetAttribute(k_filter_bulk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bk_bytes));
+      k_filter_bulk<<<B * F.blocks_per_img, kBkRows, bk_bytes, s>>>(F, stages, tile_floats);
     } else if (!F.multi_label && fb_smem <= 160 * 1024) {
       // best-class mode: one thread per row over a staged tile
       int bpi2 = (num_sms() * 8 + B - 1) / B;
