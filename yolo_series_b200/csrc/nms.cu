@@ -583,6 +583,7 @@ struct NmsParams {
   int thr_nonneg;
   float* out;            // [B][max_det][6]
   int* counts_out;       // [B]
+  int band_cap;          // keys per band (<= kBandCap): sized with the shared memory of the launch
 };
 
 __device__ __forceinline__ bool iou_suppresses(float ix1, float iy1, float ix2, float iy2, float iarea,
@@ -613,7 +614,7 @@ __device__ uint64_t* block_radix_sort(uint64_t* src, uint64_t* dst, int n, int* 
   if (tid == 0) { s_and = ~0ull; s_or = 0ull; }
   __syncthreads();
   unsigned long long a = ~0ull, o = 0ull;
-  for (int i = tid; i < n; i += kSortThreads) { unsigned long long k = src[i]; a &= k; o |= k; }
+  for (int i = tid; i < n; i += (int)blockDim.x) { unsigned long long k = src[i]; a &= k; o |= k; }
 #pragma unroll
   for (int s = 16; s > 0; s >>= 1) {
     a &= __shfl_xor_sync(0xffffffffu, a, s);
@@ -623,12 +624,12 @@ __device__ uint64_t* block_radix_sort(uint64_t* src, uint64_t* dst, int n, int* 
   __syncthreads();
   const unsigned long long varying = s_and ^ s_or;
   // contiguous segment of the array owned by each warp (keeps the scatter stable)
-  const int per_warp = ((n + kSortWarps - 1) / kSortWarps + 31) / 32 * 32;
+  const int per_warp = ((n + ((int)blockDim.x >> 5) - 1) / ((int)blockDim.x >> 5) + 31) / 32 * 32;
   const int seg0 = min(n, warp * per_warp), seg1 = min(n, seg0 + per_warp);
   for (int pass = 0; pass < 8 && n > 1; ++pass) {
     const int sh = pass * 8;
     if (((varying >> sh) & 0xffull) == 0) continue;  // digit identical for every key
-    for (int i = tid; i < kSortWarps * 256; i += kSortThreads) whist[i] = 0;
+    for (int i = tid; i < ((int)blockDim.x >> 5) * 256; i += (int)blockDim.x) whist[i] = 0;
     __syncthreads();
     int* myh = whist + warp * 256;
     for (int i = seg0 + lane; i - lane < seg1; i += 32) {
@@ -642,7 +643,7 @@ __device__ uint64_t* block_radix_sort(uint64_t* src, uint64_t* dst, int n, int* 
     // exclusive scan in (digit major, warp minor) order: thread t<256 owns digit t
     if (tid < 256) {
       int s = 0;
-      for (int w = 0; w < kSortWarps; ++w) { int c = whist[w * 256 + tid]; whist[w * 256 + tid] = s; s += c; }
+      for (int w = 0; w < ((int)blockDim.x >> 5); ++w) { int c = whist[w * 256 + tid]; whist[w * 256 + tid] = s; s += c; }
       digit_tot[tid] = s;
     }
     __syncthreads();
@@ -659,7 +660,7 @@ __device__ uint64_t* block_radix_sort(uint64_t* src, uint64_t* dst, int n, int* 
     __syncthreads();
     if (tid < 256) {
       const int base = digit_tot[tid];
-      for (int w = 0; w < kSortWarps; ++w) whist[w * 256 + tid] += base;
+      for (int w = 0; w < ((int)blockDim.x >> 5); ++w) whist[w * 256 + tid] += base;
     }
     __syncthreads();
     for (int i = seg0 + lane; i - lane < seg1; i += 32) {
@@ -686,7 +687,8 @@ __device__ uint64_t* block_radix_sort(uint64_t* src, uint64_t* dst, int n, int* 
 // three digit levels (12 + 12 + 8 bits) while that count exceeds kBandCap.  If fewer than kBandMin keys are left,
 // T = 0xffffffff takes them all.  Returns the band size through s_out[0] and T through s_out[1].
 // hist: 4096 ints of scratch.
-__device__ void select_band(const uint64_t* keys, int n, uint32_t lo, bool have_lo, int* hist, uint32_t* s_out) {
+__device__ void select_band(const uint64_t* keys, int n, uint32_t lo, bool have_lo, int* hist, uint32_t* s_out,
+                            int band_cap) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   __shared__ int s_wsum[kSortWarps];
   __shared__ int s_found, s_bin, s_cum_in, s_cum_ex, s_total;
@@ -697,10 +699,10 @@ __device__ void select_band(const uint64_t* keys, int n, uint32_t lo, bool have_
     const int shift = level == 0 ? 20 : level == 1 ? 8 : 0;
     const int nbins = 1 << nb;
     __syncthreads();
-    for (int i = tid; i < nbins; i += kSortThreads) hist[i] = 0;
+    for (int i = tid; i < nbins; i += (int)blockDim.x) hist[i] = 0;
     if (tid == 0) s_found = 0;
     __syncthreads();
-    for (int i = tid; i < n; i += kSortThreads) {
+    for (int i = tid; i < n; i += (int)blockDim.x) {
       const uint32_t h = (uint32_t)(keys[i] >> 32);
       if (have_lo && h <= lo) continue;
       if (pbits && (h >> (32 - pbits)) != prefix) continue;
@@ -708,8 +710,8 @@ __device__ void select_band(const uint64_t* keys, int n, uint32_t lo, bool have_
     }
     __syncthreads();
     // block scan: thread t owns bins [per*t, per*t + per)
-    const int per = nbins / kSortThreads > 0 ? nbins / kSortThreads : 1;
-    int loc[4] = {0, 0, 0, 0};
+    const int per = nbins / (int)blockDim.x > 0 ? nbins / (int)blockDim.x : 1;
+    int loc[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // per <= 4096 / 512
     int sum = 0;
     if (tid * per < nbins) {
       for (int q = 0; q < per; ++q) { loc[q] = hist[tid * per + q]; sum += loc[q]; }
@@ -720,7 +722,7 @@ __device__ void select_band(const uint64_t* keys, int n, uint32_t lo, bool have_
     if (lane == 31) s_wsum[warp] = incl;
     __syncthreads();
     if (warp == 0) {
-      int v = s_wsum[lane], x = v;
+      int v = lane < ((int)blockDim.x >> 5) ? s_wsum[lane] : 0, x = v;
 #pragma unroll
       for (int s = 1; s < 32; s <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, s); if (lane >= s) x += y; }
       s_wsum[lane] = x - v;
@@ -742,7 +744,7 @@ __device__ void select_band(const uint64_t* keys, int n, uint32_t lo, bool have_
       return;
     }
     const uint32_t j = (uint32_t)s_bin;
-    if (s_cum_in <= kBandCap || level == 2) {
+    if (s_cum_in <= band_cap || level == 2) {
       if (tid == 0) {
         s_out[0] = (uint32_t)s_cum_in;
         s_out[1] = (((prefix << nb) | j) << shift) | ((shift ? (1u << shift) : 1u) - 1u);
@@ -760,6 +762,7 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int b = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31;
+  const int parts = (int)blockDim.x / kChunk, pshift = parts == 4 ? 2 : 1;   // threads per candidate in phases A/B
   int n = P.count[b];
   if (n > P.cap) n = P.cap;
   uint64_t* gkeys = P.keys_a + (size_t)b * P.cap;
@@ -787,8 +790,9 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
   __shared__ uint32_t s_sel[2];
   const size_t nms_bytes = (size_t)((calive + kChunk) - smem_raw + 15) / 16 * 16;
   uint64_t* band_a = reinterpret_cast<uint64_t*>(smem_raw + nms_bytes);
-  uint64_t* band_b = band_a + kBandCap;
-  int* scratch = reinterpret_cast<int*>(band_b + kBandCap);   // radix histograms [kSortWarps][256] / select [4096]
+  const int band_cap = P.band_cap;
+  uint64_t* band_b = band_a + band_cap;
+  int* scratch = reinterpret_cast<int*>(band_b + band_cap);   // radix histograms [((int)blockDim.x >> 5)][256] / select [4096]
   if (tid == 0) s_K = 0;
   __syncthreads();
 
@@ -801,14 +805,14 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
     const uint64_t* src;
     int band_n;
     uint32_t T = 0xffffffffu;
-    if (!have_lo && n <= kBandCap) {
+    if (!have_lo && n <= band_cap) {
       band_n = n;
     } else {
-      select_band(gkeys, n, lo, have_lo, scratch, s_sel);
+      select_band(gkeys, n, lo, have_lo, scratch, s_sel, band_cap);
       band_n = (int)s_sel[0];
       T = s_sel[1];
     }
-    if (band_n > kBandCap) {
+    if (band_n > band_cap) {
       // more equal scores than a band holds: sort everything once in global memory and walk the rest of it
       // (the `consumed` smallest keys are exactly the bands already processed)
       src = block_radix_sort(gkeys, gtmp, n, scratch) + consumed;
@@ -817,7 +821,7 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       __syncthreads();
       if (tid == 0) s_cnt = 0;
       __syncthreads();
-      for (int i0 = 0; i0 < n; i0 += kSortThreads) {
+      for (int i0 = 0; i0 < n; i0 += (int)blockDim.x) {
         const int i = i0 + tid;
         unsigned long long key = 0ull;
         bool sel = false;
@@ -862,18 +866,18 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       cconf[tid] = conf; ccls[tid] = (float)cls;
     }
     __syncthreads();
-    // ---- phase A: candidate j vs every kept box (4 threads per candidate)
+    // ---- phase A: candidate j vs every kept box (parts = blockDim / kChunk = 4 or 2 threads per candidate)
     {
-      const int j = tid >> 2, part = tid & 3;
+      const int j = tid >> pshift, part = tid & (parts - 1);
       bool sup = false;
       if (j < cnt) {
         const float jx1 = cx1[j], jy1 = cy1[j], jx2 = cx2[j], jy2 = cy2[j], ja = car[j];
-        for (int k = part; k < K && !sup; k += 4)
+        for (int k = part; k < K && !sup; k += parts)
           sup = iou_suppresses(kx1[k], ky1[k], kx2[k], ky2[k], kar[k], jx1, jy1, jx2, jy2, ja, P.thr_f, P.thr_nonneg);
       }
       unsigned s = sup ? 1u : 0u;
       s |= __shfl_xor_sync(0xffffffffu, s, 1);
-      s |= __shfl_xor_sync(0xffffffffu, s, 2);
+      if (parts == 4) s |= __shfl_xor_sync(0xffffffffu, s, 2);
       if (part == 0) calive[j] = (j < cnt && !s) ? 1 : 0;
     }
     __syncthreads();
@@ -885,10 +889,10 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
     }
     // ---- phase B: intra-chunk suppression bit matrix, rows of live candidates only
     {
-      const int i = tid >> 2, part = tid & 3;
+      const int i = tid >> pshift, part = tid & (parts - 1);
       if (i < cnt && calive[i]) {
         const float ix1 = cx1[i], iy1 = cy1[i], ix2 = cx2[i], iy2 = cy2[i], ia = car[i];
-        for (int w = part; w < kChunkWords; w += 4) {
+        for (int w = part; w < kChunkWords; w += parts) {
           uint32_t word = 0;
           const int j0 = w * 32;
           if (j0 + 31 > i) {
@@ -1108,9 +1112,20 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
   N.thr_f = T; N.thr_nonneg = (T >= 0.0f) ? 1 : 0;
   N.out = out; N.counts_out = counts;
   size_t sm_nms = (size_t)max_det * 5 * 4 + (size_t)kChunk * (5 + 4 + 2) * 4 + (size_t)kChunk * kChunkWords * 4 + kChunk;
-  size_t smem = (sm_nms + 15) / 16 * 16 + 2 * (size_t)kBandCap * 8 + (size_t)kSortWarps * 256 * 4;
+  // More images than SMs: 512-thread CTAs with 3072-key bands fit two per SM, so the whole batch is resident at once
+  // and one CTA's serial phases hide behind the other's; otherwise one 1024-thread CTA per image.
+  int threads = kSortThreads;
+  N.band_cap = kBandCap;
+  static const char* force = getenv("YB_NMS_SORT_THREADS");
+  const size_t smem_half = (sm_nms + 15) / 16 * 16 + 2 * (size_t)3072 * 8 + (size_t)4096 * 4;
+  if ((force ? atoi(force) == 512 : B > num_sms()) && smem_half <= 112 * 1024) {
+    threads = 512;
+    N.band_cap = 3072;
+  }
+  const size_t hist_bytes = (size_t)(threads / 32) * 256 * 4 > 4096 * 4 ? (size_t)(threads / 32) * 256 * 4 : 4096 * 4;
+  size_t smem = (sm_nms + 15) / 16 * 16 + 2 * (size_t)N.band_cap * 8 + hist_bytes;
   YB_CUDA(cudaFuncSetAttribute(k_sort_nms, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  k_sort_nms<<<B, kSortThreads, smem, s>>>(N);
+  k_sort_nms<<<B, threads, smem, s>>>(N);
   YB_LAUNCH_CHECK();
   return YB_OK;
 }
