@@ -179,6 +179,11 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--batch', type=int, default=BATCH, help='images per GPU per step')
     ap.add_argument('--no-extras', action='store_true', help='skip cpu_baseline / NMS stress / per-op profile')
+    # secondary BASELINE.json configs (configs[2], configs[3]); the defaults are the headline workload
+    ap.add_argument('--model', default=MODEL, help='cfg name (yolov7 | yolov7-tiny | yolov7-w6-custom | yolov7-e6e)')
+    ap.add_argument('--img', type=int, default=IMG)
+    ap.add_argument('--global-batch', type=int, default=0,
+                    help='fixed global batch sharded image-wise over the ranks (strong scaling); 0 = --batch per rank (weak)')
     args = ap.parse_args()
     rank = int(os.environ.get('RANK', 0))
     world = int(os.environ.get('WORLD_SIZE', 1))
@@ -197,10 +202,18 @@ def main():
         dist.init_process_group('nccl', device_id=dev)
     peaks, peak_src = load_peaks()
     B = args.batch
-    model = Model(MODEL)
+    model_name, img = args.model, args.img
+    scaling = 'weak'
+    if args.global_batch:
+        lo, hi = ydist.shard_bounds(args.global_batch, rank, world)
+        if (hi - lo) * world != args.global_batch:
+            raise SystemExit('--global-batch must divide evenly over the ranks (equal shards for the all-gather)')
+        B, scaling = hi - lo, 'strong'
+    headline = (model_name, img) == (MODEL, IMG)
+    model = Model(model_name)
     model.load_state_dict(seeded_state_dict(model, seed=0))
     model = model.to(dev).eval().half()          # bf16 trunk (reference: model.half(), detect.py:49)
-    x_host = synth_image(B, IMG, IMG, seed=100 + rank, dtype=torch.uint8).pin_memory()
+    x_host = synth_image(B, img, img, seed=100 + rank, dtype=torch.uint8).pin_memory()
     x_dev = x_host.to(dev)
 
     def step_device():
@@ -275,13 +288,13 @@ def main():
     n_imgs = B * world * args.steps
     launches_per_step = 1 + eng.num_launches() + 2     # stage + trunk ops + k_filter + k_sort_nms
     line = {
-        'metric': 'yolov7 640 bf16 e2e images/sec (forward+decode+NMS)', 'value': n_imgs / (ms_dev / 1e3),
+        'metric': f'{model_name} {img} bf16 e2e images/sec (forward+decode+NMS)', 'value': n_imgs / (ms_dev / 1e3),
         'unit': 'images/s', 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
-        'ms_per_step': ms_dev / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'ms_per_step': ms_dev / args.steps, 'higher_is_better': True, 'scaling': scaling, 'vs_baseline': None,
         'dtype': 'bf16', 'data': 'synthetic',
-        'config': {'workload': f'{MODEL} {IMG}x{IMG} batch {B}/GPU bf16, RepConv/BN folded, conf {CONF} iou {IOU} max_det {MAX_DET}',
+        'config': {'workload': f'{model_name} {img}x{img} batch {B}/GPU bf16, RepConv/BN folded, conf {CONF} iou {IOU} max_det {MAX_DET}',
                    'batch_per_gpu': B, 'global_batch': B * world, 'parallelism': f'image-sharded replicas x{world}',
-                   'l2': 'no flush: per-step working set (activations) 5.5 GB >> 126 MB L2'},
+                   'l2': 'no flush: per-step working set (activations, GBs) >> 126 MB L2'},
         'e2e': {'value': n_imgs / (ms_e2e / 1e3), 'unit': 'images/s', 'h2d_bytes_per_step': x_host.numel(),
                 'd2h_bytes_per_step': int(res.numel() * 4 + cnt.numel() * 4 + 4), 'ms_per_step': ms_e2e / args.steps,
                 'api': 'Model.detect_batches (H2D / compute / D2H on three streams, two slots)',
@@ -300,7 +313,9 @@ def main():
         ach = flops / (conv_ms / 1e3) / 1e12
         n_conv = sum(1 for r in prof if r[1] == 1)
         traffic, traffic_src = None, None
-        try:   # DRAM bytes of the conv launches of one step, from the committed ncu launch list (cold-cache per launch)
+        try:   # (headline workload only) DRAM bytes of the conv launches of one step, from the committed ncu launch list (cold-cache per launch)
+            if not headline:
+                raise KeyError('launch list exists for the headline workload only')
             summ = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles',
                                                'round1_launch_summary.json')))
             traffic = summ['conv_dram_bytes_per_step']
@@ -316,7 +331,7 @@ def main():
                             'conv_share_of_trunk': conv_ms / all_ms}
         top = sorted(prof, key=lambda r: -r[2])[:8]
         line['top_ops'] = [{'op': r[0], 'ms': round(r[2], 4), 'tflops': round(r[3] / r[2] / 1e9, 1) if r[3] else None} for r in top]
-        if world == 1:
+        if world == 1 and headline:
             try:
                 line['nms_stress'] = nms_stress(dev, peaks)
             except Exception as ex:  # noqa: BLE001
