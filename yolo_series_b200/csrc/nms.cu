@@ -601,6 +601,10 @@ __device__ __forceinline__ bool iou_suppresses(float ix1, float iy1, float ix2, 
 // (at least kBandMin keys, at most kBandCap so that it sorts inside shared memory), sorted, and fed to the greedy
 // loop, which usually reaches max_det inside the first band.  Bands are disjoint key ranges taken in key order and
 // every key is distinct, so the sequence of candidates is exactly that of one full sort (general.py:695-699).
+constexpr int kBuckets = 128;            // class buckets of the kept set (k_sort_nms)
+constexpr float kBucketExtent = 4000.0f; // < kMaxWH with room for the rounding of x + cls * 4096
+__device__ __forceinline__ int ordered_int(float f) { const int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__device__ __forceinline__ float ordered_float(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 constexpr int kBandMin = 1024;
 constexpr int kBandCap = 4096;
 
@@ -784,16 +788,29 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
   float* cconf = craw + 4 * kChunk;
   float* ccls = cconf + kChunk;
   uint32_t* cmask = reinterpret_cast<uint32_t*>(ccls + kChunk);  // [kChunk][kChunkWords]
-  unsigned char* calive = reinterpret_cast<unsigned char*>(cmask + kChunk * kChunkWords);
+  uint32_t* kmeta = cmask + kChunk * kChunkWords;   // [max_det] class << 16 | next kept box of the same class bucket
+  unsigned char* calive = reinterpret_cast<unsigned char*>(kmeta + P.max_det);
   __shared__ uint32_t s_alive[kChunkWords], s_new[kChunkWords];
   __shared__ int s_K, s_cnt;
   __shared__ uint32_t s_sel[2];
+  // Class buckets: with the 4096-px class offset (general.py:702) two boxes of different classes cannot intersect as
+  // long as the un-offset x extent of everything seen so far stays below kBucketExtent, so a candidate only needs the
+  // kept boxes of its own class.  Kept boxes are chained per bucket (class & 127); the mode is dropped for good (full
+  // scan of the kept set, always correct) if the extent grows beyond the limit, for agnostic NMS, or a negative threshold.
+  __shared__ int s_khead[kBuckets], s_kcnt[kBuckets];
+  __shared__ int s_bucket_ok, s_xmin, s_xmax;
   const size_t nms_bytes = (size_t)((calive + kChunk) - smem_raw + 15) / 16 * 16;
   uint64_t* band_a = reinterpret_cast<uint64_t*>(smem_raw + nms_bytes);
   const int band_cap = P.band_cap;
   uint64_t* band_b = band_a + band_cap;
   int* scratch = reinterpret_cast<int*>(band_b + band_cap);   // radix histograms [((int)blockDim.x >> 5)][256] / select [4096]
-  if (tid == 0) s_K = 0;
+  if (tid == 0) {
+    s_K = 0;
+    s_bucket_ok = (P.thr_nonneg && !P.agnostic && P.max_det < 0xffff) ? 1 : 0;
+    s_xmin = 0x7fffffff;
+    s_xmax = (int)0x80000000;
+  }
+  if (tid < kBuckets) { s_khead[tid] = 0xffff; s_kcnt[tid] = 0; }
   __syncthreads();
 
   int consumed = 0;
@@ -848,6 +865,7 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
     if (K >= P.max_det) break;
     const int cnt = min(kChunk, m - base);
     // ---- load chunk: un-offset xyxy, class offset, offset boxes + area (general.py:676,702-703)
+    int ex_lo = 0x7fffffff, ex_hi = (int)0x80000000;
     if (tid < cnt) {
       const unsigned long long key = src[base + tid];
       const uint32_t idx = (uint32_t)key;
@@ -864,16 +882,40 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       car[tid] = __fmul_rn(__fsub_rn(ox2, ox1), __fsub_rn(oy2, oy1));
       craw[4 * tid + 0] = x1; craw[4 * tid + 1] = y1; craw[4 * tid + 2] = x2; craw[4 * tid + 3] = y2;
       cconf[tid] = conf; ccls[tid] = (float)cls;
+      if (x1 != x1 || x2 != x2) s_bucket_ok = 0;
+      ex_lo = ordered_int(x1);
+      ex_hi = ordered_int(x2);
+    }
+    if (tid < kChunk) {      // whole warps: one shared-memory atomic per warp instead of one per candidate
+      ex_lo = __reduce_min_sync(0xffffffffu, ex_lo);
+      ex_hi = __reduce_max_sync(0xffffffffu, ex_hi);
+      if (lane == 0) { atomicMin(&s_xmin, ex_lo); atomicMax(&s_xmax, ex_hi); }
     }
     __syncthreads();
+    if (tid == 0 && s_bucket_ok && !(__fsub_rn(ordered_float(s_xmax), ordered_float(s_xmin)) <= kBucketExtent)) s_bucket_ok = 0;
+    __syncthreads();
+    const bool bucket_mode = s_bucket_ok != 0;
     // ---- phase A: candidate j vs every kept box (parts = blockDim / kChunk = 4 or 2 threads per candidate)
     {
       const int j = tid >> pshift, part = tid & (parts - 1);
       bool sup = false;
       if (j < cnt) {
         const float jx1 = cx1[j], jy1 = cy1[j], jx2 = cx2[j], jy2 = cy2[j], ja = car[j];
-        for (int k = part; k < K && !sup; k += parts)
-          sup = iou_suppresses(kx1[k], ky1[k], kx2[k], ky2[k], kar[k], jx1, jy1, jx2, jy2, ja, P.thr_f, P.thr_nonneg);
+        const uint32_t cj = (uint32_t)ccls[j];
+        // every thread of the candidate walks the whole chain (dependent loads), so the chain only pays when it is
+        // much shorter than this thread's share of the kept array (one dominant class -> array scan)
+        if (bucket_mode && s_kcnt[cj & (kBuckets - 1)] * parts * 2 <= K) {
+          int k = s_khead[cj & (kBuckets - 1)], t = 0;
+          while (k != 0xffff && !sup) {
+            const uint32_t meta = kmeta[k];
+            if ((meta >> 16) == cj && (t++ & (parts - 1)) == part)
+              sup = iou_suppresses(kx1[k], ky1[k], kx2[k], ky2[k], kar[k], jx1, jy1, jx2, jy2, ja, P.thr_f, P.thr_nonneg);
+            k = (int)(meta & 0xffffu);
+          }
+        } else {
+          for (int k = part; k < K && !sup; k += parts)
+            sup = iou_suppresses(kx1[k], ky1[k], kx2[k], ky2[k], kar[k], jx1, jy1, jx2, jy2, ja, P.thr_f, P.thr_nonneg);
+        }
       }
       unsigned s = sup ? 1u : 0u;
       s |= __shfl_xor_sync(0xffffffffu, s, 1);
@@ -891,14 +933,14 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
     {
       const int i = tid >> pshift, part = tid & (parts - 1);
       if (i < cnt && calive[i]) {
-        const float ix1 = cx1[i], iy1 = cy1[i], ix2 = cx2[i], iy2 = cy2[i], ia = car[i];
+        const float ix1 = cx1[i], iy1 = cy1[i], ix2 = cx2[i], iy2 = cy2[i], ia = car[i], ci = ccls[i];
         for (int w = part; w < kChunkWords; w += parts) {
           uint32_t word = 0;
           const int j0 = w * 32;
           if (j0 + 31 > i) {
             for (int q = 0; q < 32; ++q) {
               const int j = j0 + q;
-              if (j > i && j < cnt && calive[j] &&
+              if (j > i && j < cnt && calive[j] && (!bucket_mode || ccls[j] == ci) &&
                   iou_suppresses(ix1, iy1, ix2, iy2, ia, cx1[j], cy1[j], cx2[j], cy2[j], car[j], P.thr_f, P.thr_nonneg))
                 word |= 1u << q;
             }
@@ -935,6 +977,11 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       int pos = K + __popc(s_new[tid >> 5] & ((1u << (tid & 31)) - 1u));
       for (int w = 0; w < (tid >> 5); ++w) pos += __popc(s_new[w]);
       kx1[pos] = cx1[tid]; ky1[pos] = cy1[tid]; kx2[pos] = cx2[tid]; ky2[pos] = cy2[tid]; kar[pos] = car[tid];
+      if (bucket_mode) {
+        const uint32_t cj = (uint32_t)ccls[tid];
+        kmeta[pos] = (cj << 16) | (uint32_t)atomicExch(&s_khead[cj & (kBuckets - 1)], pos);
+        atomicAdd(&s_kcnt[cj & (kBuckets - 1)], 1);
+      }
       float* o = P.out + ((size_t)b * P.max_det + pos) * 6;
       o[0] = craw[4 * tid + 0]; o[1] = craw[4 * tid + 1]; o[2] = craw[4 * tid + 2]; o[3] = craw[4 * tid + 3];
       o[4] = cconf[tid]; o[5] = ccls[tid];
@@ -1111,7 +1158,7 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
   if ((double)T > iou_thres) T = nextafterf(T, -INFINITY);
   N.thr_f = T; N.thr_nonneg = (T >= 0.0f) ? 1 : 0;
   N.out = out; N.counts_out = counts;
-  size_t sm_nms = (size_t)max_det * 5 * 4 + (size_t)kChunk * (5 + 4 + 2) * 4 + (size_t)kChunk * kChunkWords * 4 + kChunk;
+  size_t sm_nms = (size_t)max_det * 6 * 4 + (size_t)kChunk * (5 + 4 + 2) * 4 + (size_t)kChunk * kChunkWords * 4 + kChunk;
   // More images than SMs: 512-thread CTAs with 3072-key bands fit two per SM, so the whole batch is resident at once
   // and one CTA's serial phases hide behind the other's; otherwise one 1024-thread CTA per image.
   int threads = kSortThreads;
