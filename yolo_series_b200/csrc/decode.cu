@@ -33,29 +33,45 @@ struct DecodeLevel {
   int flip;
 };
 
+// Block = one run of kDecCells cells of one (image, grid row); thread = channel c of the cell (c = a*no + o, strided
+// by the block size when na*no > 256).  Loads are coalesced over the channels of a cell, stores are na runs of `no`
+// contiguous floats per cell; no integer division anywhere (a is found by comparison, na <= 8).  The kDecCells loads
+// of a thread are issued before any arithmetic.
+constexpr int kDecCells = 8;
+
 template <typename T>
 __global__ void __launch_bounds__(256) k_decode(DecodeLevel L, int B, int A, int na, int no, float* __restrict__ pred) {
   const int C = na * no;
-  const size_t total = (size_t)B * L.ny * L.nx * C;
-  const T* in = reinterpret_cast<const T*>(L.logits);
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    int c = (int)(i % C);
-    size_t p = i / C;
-    int x = (int)(p % L.nx);
-    size_t q = p / L.nx;
-    int y = (int)(q % L.ny);
-    int b = (int)(q / L.ny);
-    float t = Elem<T>::load(in + p * L.c_stride + c);
-    int a = c / no, o = c - a * no;
-    float v = decode_elem(sigmoid_rn(t), o, x, y, L.stride, L.anchor_wh[2 * a], L.anchor_wh[2 * a + 1]);
-    if (o < 4) {
-      if (L.scale != 1.0f) v = __fdiv_rn(v, L.scale);
-      if (o == 1 && L.flip == 2) v = __fsub_rn(L.img_h, v);
-      if (o == 0 && L.flip == 3) v = __fsub_rn(L.img_w, v);
+  const int y = blockIdx.x % L.ny, b = blockIdx.x / L.ny;
+  const int x0 = blockIdx.y * kDecCells;
+  const int ncell = min(kDecCells, L.nx - x0);
+  const T* in = reinterpret_cast<const T*>(L.logits) + ((size_t)(b * L.ny + y) * L.nx + x0) * L.c_stride;
+  const size_t plane = (size_t)L.ny * L.nx;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    int a = 0;
+#pragma unroll
+    for (int q = 1; q < YB_MAX_ANCHORS; ++q) a += (q < na && c >= q * no) ? 1 : 0;
+    const int o = c - a * no;
+    const float aw = L.anchor_wh[2 * a], ah = L.anchor_wh[2 * a + 1];
+    float t[kDecCells];
+#pragma unroll
+    for (int i = 0; i < kDecCells; ++i) t[i] = i < ncell ? Elem<T>::load(in + (size_t)i * L.c_stride + c) : 0.0f;
+    const size_t cell0 = ((size_t)a * L.ny + y) * L.nx + x0;
+    float* prow = pred + ((size_t)b * A + L.row_off + cell0) * no + o;
+    float* rrow = L.raw ? L.raw + ((size_t)b * na * plane + cell0) * no + o : nullptr;
+#pragma unroll
+    for (int i = 0; i < kDecCells; ++i) {
+      if (i < ncell) {
+        float v = decode_elem(sigmoid_rn(t[i]), o, x0 + i, y, L.stride, aw, ah);
+        if (o < 4) {
+          if (L.scale != 1.0f) v = __fdiv_rn(v, L.scale);
+          if (o == 1 && L.flip == 2) v = __fsub_rn(L.img_h, v);
+          if (o == 0 && L.flip == 3) v = __fsub_rn(L.img_w, v);
+        }
+        prow[(size_t)i * no] = v;
+        if (rrow) rrow[(size_t)i * no] = t[i];
+      }
     }
-    size_t cell = ((size_t)a * L.ny + y) * L.nx + x;
-    pred[((size_t)b * A + L.row_off + cell) * no + o] = v;
-    if (L.raw) L.raw[(((size_t)b * na) * L.ny * L.nx + cell) * no + o] = t;
   }
 }
 
@@ -95,9 +111,8 @@ static int decode_impl(const yb_head_level* levels, int nl, int na, int no, floa
     L.flip = pass ? pass->flip : 0;
     L.img_h = pass ? pass->img_h : 0.0f;
     L.img_w = pass ? pass->img_w : 0.0f;
-    size_t total = (size_t)B * t.H * t.W * na * no;
-    size_t g = (total + 255) / 256, cap = (size_t)num_sms() * 16;
-    int grid = (int)(g < cap ? g : cap);
+    YB_CHECK_ARG(ceil_div(t.W, kDecCells) <= 65535, "yb_decode: level %d is too wide", l);
+    dim3 grid((unsigned)(B * t.H), (unsigned)ceil_div(t.W, kDecCells));
     if (t.dtype == YB_F32) k_decode<float><<<grid, 256, 0, (cudaStream_t)stream>>>(L, B, rows, na, no, pred);
     else k_decode<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(L, B, rows, na, no, pred);
     YB_LAUNCH_CHECK();
