@@ -140,3 +140,34 @@ def test_repconv_identity_branch_fold():
         fc = fold.fold_repconv(m)
         got = F.silu(F.conv2d(x, fc.weight, fc.bias, 1, 1))
     assert torch.allclose(got, ref, atol=1e-5)
+
+
+def test_tta_pass_geometry_matches_reference_shapes(gold):
+    """Model._passes / rows_per_image reproduce scale_img's sizes (torch_utils.py:247-257) and the row count of the
+    reference's augmented output (tests/golden/tta_tiny.npz, tta_scale_img.npz)."""
+    m = Model('yolov7-tiny')
+    assert m.rows_per_image(128, 160) == 1260
+    assert m.rows_per_image(128, 160, augment=True) == gold('tta_tiny.npz')['pred'].shape[1] == 3276
+    p = m._passes(96, 136, True)
+    g = gold('tta_scale_img.npz')
+    assert [q[0] for q in p] == [1, 0.83, 0.67] and [q[1] for q in p] == [None, 3, None]
+    assert p[1][3] == g['r0.83_fNone'].shape[2:] and p[2][3] == g['r0.67_fNone'].shape[2:]
+    assert p[1][2] == (int(96 * 0.83), int(136 * 0.83))
+    w6 = Model('yolov7-w6-custom')                       # gs = 64 for the four-level heads
+    assert [q[3] for q in w6._passes(1280, 1280, True)] == [(1280, 1280), (1088, 1088), (896, 896)]
+    assert w6.rows_per_image(1280, 1280) == 102000
+
+
+def test_ensemble_and_eval_surface_without_gpu():
+    from yolo_series_b200 import Ensemble
+    from yolo_series_b200 import evaluate
+    ens = Ensemble([Model('yolov7-tiny'), Model('yolov7-tiny')])
+    assert len(ens) == 2 and ens.stride.tolist() == [8., 16., 32.] and len(ens.names) == 80
+    with pytest.raises(RuntimeError):
+        ens(torch.zeros(1, 3, 64, 64))                   # no CPU fallback
+    with pytest.raises(RuntimeError):
+        evaluate.box_iou(torch.zeros(2, 4), torch.zeros(3, 4))
+    with pytest.raises(RuntimeError):
+        evaluate.match_batch(torch.zeros(1, 4, 6), torch.zeros(1, dtype=torch.int32), torch.zeros(0, 6), (64, 64),
+                             [dict(shape0=(64, 64), ratio=(1, 1), pad=(0, 0))], torch.linspace(0.5, 0.95, 10))
+    assert evaluate.NMS.conf == 0.25 and evaluate.NMS.iou == 0.45 and evaluate.autoShape.classes is None
