@@ -216,17 +216,22 @@ def main():
     x_host = synth_image(B, img, img, seed=100 + rank, dtype=torch.uint8).pin_memory()
     x_dev = x_host.to(dev)
 
+    # N > 1: the one exchange of the path (every rank's detections to every rank) happens inside the NMS kernel through
+    # peer-to-peer stores over NVLink (dist.PeerGather); YB_GATHER=nccl selects the plain NCCL all-gather instead.
+    use_peer = world > 1 and os.environ.get('YB_GATHER', 'peer') != 'nccl'
+    pg = ydist.PeerGather(B, MAX_DET, device=dev) if use_peer else None
+
     def step_device():
-        out, meta = model.detect(x_dev, CONF, IOU, max_det=MAX_DET, packed=True)
-        if world > 1:
+        out, meta = model.detect(x_dev, CONF, IOU, max_det=MAX_DET, packed=True, gather=pg)
+        if world > 1 and pg is None:
             out, cnt = ydist.gather_detections(out, meta[:B])
         return out, meta
 
     def step_e2e():
         # the pinned host batch is copied H2D straight into the engine's input buffer, every step
-        out, meta = model.detect(x_host, CONF, IOU, max_det=MAX_DET, packed=True)
-        cnt = meta[:B]
-        if world > 1:
+        out, meta = model.detect(x_host, CONF, IOU, max_det=MAX_DET, packed=True, gather=pg)
+        cnt = meta[:-1]
+        if world > 1 and pg is None:
             out, cnt = ydist.gather_detections(out, cnt)
         return out.cpu(), cnt.cpu()                               # D2H read of the step's result
 
@@ -262,11 +267,11 @@ def main():
     ms_e2e_serial = e0.elapsed_time(e1)
     # the same through the streaming API (Model.detect_batches): every step still copies its own pinned host
     # batch H2D and reads its own detections back D2H, but on copy streams that overlap the neighbouring steps
-    post = (lambda o, c: ydist.gather_detections(o, c)) if world > 1 else None
+    post = (lambda o, c: ydist.gather_detections(o, c)) if (world > 1 and pg is None) else None
 
     def run_stream(n):
         last = None
-        for last in model.detect_batches((x_host for _ in range(n)), CONF, IOU, max_det=MAX_DET, post=post):
+        for last in model.detect_batches((x_host for _ in range(n)), CONF, IOU, max_det=MAX_DET, post=post, gather=pg):
             pass
         return last
     run_stream(3)
@@ -280,6 +285,9 @@ def main():
         t = torch.tensor([ms_dev, ms_e2e, ms_e2e_serial], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_dev, ms_e2e, ms_e2e_serial = float(t[0]), float(t[1]), float(t[2])
+    if pg is not None:
+        pg.check()
+        pg.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -294,6 +302,8 @@ def main():
         'dtype': 'bf16', 'data': 'synthetic',
         'config': {'workload': f'{model_name} {img}x{img} batch {B}/GPU bf16, RepConv/BN folded, conf {CONF} iou {IOU} max_det {MAX_DET}',
                    'batch_per_gpu': B, 'global_batch': B * world, 'parallelism': f'image-sharded replicas x{world}',
+                   'gather': ('none' if world == 1 else 'in-kernel P2P stores over NVLink (yb_decode_nms_gather)' if use_peer
+                              else 'NCCL all_gather'),
                    'l2': 'no flush: per-step working set (activations, GBs) >> 126 MB L2'},
         'e2e': {'value': n_imgs / (ms_e2e / 1e3), 'unit': 'images/s', 'h2d_bytes_per_step': x_host.numel(),
                 'd2h_bytes_per_step': int(res.numel() * 4 + cnt.numel() * 4 + 4), 'ms_per_step': ms_e2e / args.steps,

@@ -158,6 +158,39 @@ int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no, float con
                   int max_nms, int max_det, int cand_cap, void* workspace, size_t workspace_bytes,
                   float* out, int* counts, int* overflow, void* stream);
 
+/* ------------------------------------------------------------------ multi-GPU gather fused into NMS
+ * Image-sharded inference ends with ONE exchange: every rank's fixed-size detection buffers go to every rank.
+ * yb_decode_nms_gather does it inside the NMS kernel: each kept row is stored, as it is produced, into the receive
+ * buffer of every GPU of the box over NVLink (peer-to-peer stores into CUDA-IPC mapped memory), and the last CTA
+ * raises the sender's arrival flag on every peer (fence.sys + st.release.sys).  yb_peer_wait is the receive side:
+ * one warp polls this rank's flags until every sender has reached `step`.  No NCCL call, no packing kernels.
+ *   out[p]    peer p's receive buffer, (n_peers, B, max_det, 6) fp32: this rank writes block `rank`
+ *   counts[p] peer p's (n_peers, B) int32;  flags[p]: peer p's (n_peers) uint32 arrival counters
+ *   step      strictly increasing per use of a buffer set (> 0); done_counter: local device int, zero-initialised
+ * Buffer sets are double-buffered by the caller (yolo_series_b200/dist.py: PeerGather).  yb_peer_alloc / open / close /
+ * free manage the cudaMalloc'd, IPC-exported regions (handle = 64-byte cudaIpcMemHandle_t).
+ */
+#define YB_MAX_PEERS 16
+typedef struct {
+  int32_t n_peers, rank;
+  float* out[YB_MAX_PEERS];
+  int32_t* counts[YB_MAX_PEERS];
+  uint32_t* flags[YB_MAX_PEERS];
+  uint32_t step;
+  int32_t* done_counter;
+} yb_peer_gather;
+
+int yb_decode_nms_gather(const yb_head_level* levels, int nl, int na, int no, float conf_thres,
+                         double iou_thres, const int* classes, int n_classes, int agnostic, int multi_label,
+                         int max_nms, int max_det, int cand_cap, void* workspace, size_t workspace_bytes,
+                         float* out, int* counts, int* overflow, const yb_peer_gather* peer /* nullable */,
+                         void* stream);
+int yb_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, int* status /* device, nullable */, void* stream);
+int yb_peer_alloc(size_t bytes, void** ptr, unsigned char handle[64]);
+int yb_peer_open(const unsigned char handle[64], void** ptr);
+int yb_peer_close(void* ptr);
+int yb_peer_free(void* ptr);
+
 /* ------------------------------------------------------------------ engine (Model.forward)
  * A flat launch list produced by the host-side graph lowering of Model.model
  * (models/yolo.py:601-631 forward_once).  Tensors and weights are caller-owned device memory.

@@ -31,16 +31,30 @@ def main():
     lo, hi = ydist.shard_bounds(G, rank, world)
     out, meta = m.detect(x[lo:hi].to(dev), 0.001, 0.65, packed=True)
     out_all, cnt_all = ydist.gather_detections(out, meta[:hi - lo])
+    # the same exchange fused into the NMS kernel (peer-to-peer stores), three steps to exercise both buffer sets
+    pg = ydist.PeerGather(hi - lo, 300, device=dev)
+    ok_peer = True
+    for _ in range(3):
+        o2, m2 = m.detect(x[lo:hi].to(dev), 0.001, 0.65, packed=True, gather=pg)
+        ok_peer = ok_peer and torch.equal(m2[:-1], cnt_all)
+        valid = torch.arange(300, device=dev)[None, :] < cnt_all[:, None]
+        ok_peer = ok_peer and torch.equal(o2[valid], out_all[valid])
+    pg.check()
+    pg.close()
+    flag = torch.tensor([int(ok_peer)], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ok_peer = bool(flag.item())
     torch.cuda.synchronize()
-    ok = True
+    ok = ok_peer
     if rank == 0:
         ref_out, ref_meta = m.detect(x.to(dev), 0.001, 0.65, packed=True)
         cnt = ref_meta[:G]
-        ok = torch.equal(cnt_all, cnt)
+        ok = ok and torch.equal(cnt_all, cnt)
         for i in range(G):
             n = int(cnt[i])
             ok = ok and torch.equal(out_all[i, :n], ref_out[i, :n])
-        print(f'dist check {name} {img} G={G} world={world}: {"bit-identical" if ok else "MISMATCH"}; '
+        print(f'dist check {name} {img} G={G} world={world}: {"bit-identical" if ok else "MISMATCH"} '
+              f'(NCCL gather == in-kernel peer gather on every rank: {ok_peer}); '
               f'detections/image mean {float(cnt.float().mean()):.1f}', flush=True)
     dist.barrier()
     dist.destroy_process_group()

@@ -21,7 +21,8 @@ EXPORTS = [
     'yb_upsample2x', 'yb_copy', 'yb_add', 'yb_stage_input', 'yb_stem_conv', 'yb_decode', 'yb_nms_workspace_bytes',
     'yb_nms', 'yb_decode_nms', 'yb_engine_create', 'yb_engine_forward', 'yb_engine_num_launches', 'yb_engine_profile',
     'yb_engine_destroy', 'yb_letterbox', 'yb_scale_coords', 'yb_scale_img', 'yb_decode_tta', 'yb_box_iou',
-    'yb_match_detections',
+    'yb_match_detections', 'yb_decode_nms_gather', 'yb_peer_wait', 'yb_peer_alloc', 'yb_peer_open', 'yb_peer_close',
+    'yb_peer_free',
 ]
 
 
@@ -56,6 +57,15 @@ class LetterboxSrc(C.Structure):
 class TtaPass(C.Structure):
     _fields_ = [('rows_total', C.c_int32), ('row_off', C.c_int32), ('scale', C.c_float), ('flip', C.c_int32),
                 ('img_h', C.c_float), ('img_w', C.c_float)]
+
+
+MAX_PEERS = 16
+
+
+class PeerGatherC(C.Structure):
+    _fields_ = [('n_peers', C.c_int32), ('rank', C.c_int32), ('out', C.c_void_p * MAX_PEERS),
+                ('counts', C.c_void_p * MAX_PEERS), ('flags', C.c_void_p * MAX_PEERS), ('step', C.c_uint32),
+                ('done_counter', C.c_void_p)]
 
 
 LAYOUT_HWC, LAYOUT_CHW = 0, 1
@@ -114,6 +124,15 @@ def lib():
     L.yb_box_iou.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
     L.yb_match_detections.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
                                       C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.yb_decode_nms_gather.argtypes = [C.POINTER(HeadLevel), C.c_int, C.c_int, C.c_int, C.c_float, C.c_double,
+                                       C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.POINTER(PeerGatherC), C.c_void_p]
+    L.yb_peer_wait.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p]
+    L.yb_peer_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]
+    L.yb_peer_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    L.yb_peer_close.argtypes = [C.c_void_p]
+    L.yb_peer_free.argtypes = [C.c_void_p]
     if L.yb_abi_version() != 1:
         raise RuntimeError('libyolo_b200.so ABI version mismatch; rebuild')
     _lib = L

@@ -584,6 +584,8 @@ struct NmsParams {
   float* out;            // [B][max_det][6]
   int* counts_out;       // [B]
   int band_cap;          // keys per band (<= kBandCap): sized with the shared memory of the launch
+  int has_peer;          // yb_decode_nms_gather: detections also go straight into every peer's receive buffer
+  yb_peer_gather peer;
 };
 
 __device__ __forceinline__ bool iou_suppresses(float ix1, float iy1, float ix2, float iy2, float iarea,
@@ -985,12 +987,52 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       float* o = P.out + ((size_t)b * P.max_det + pos) * 6;
       o[0] = craw[4 * tid + 0]; o[1] = craw[4 * tid + 1]; o[2] = craw[4 * tid + 2]; o[3] = craw[4 * tid + 3];
       o[4] = cconf[tid]; o[5] = ccls[tid];
+      if (P.has_peer) {   // the same row over NVLink into every peer's block for this rank (P2P stores; self included)
+        const size_t roff = (((size_t)P.peer.rank * P.B + b) * P.max_det + pos) * 6;
+        for (int q = 0; q < P.peer.n_peers; ++q) {
+          float* po = P.peer.out[q] + roff;
+          po[0] = o[0]; po[1] = o[1]; po[2] = o[2]; po[3] = o[3]; po[4] = o[4]; po[5] = o[5];
+        }
+      }
     }
     __syncthreads();
   }
     consumed += band_n;
   }
   if (tid == 0) P.counts_out[b] = s_K;
+  if (P.has_peer) {
+    // Completion: every CTA publishes its image, the LAST one to finish raises this rank's arrival flag on every peer
+    // (fence.sys + release store), which is what yb_peer_wait polls.  Slot reuse is the caller's protocol (dist.py).
+    __syncthreads();
+    if (tid == 0) {
+      for (int q = 0; q < P.peer.n_peers; ++q) P.peer.counts[q][P.peer.rank * P.B + b] = s_K;
+      __threadfence_system();
+      const int prev = atomicAdd(P.peer.done_counter, 1);
+      if (prev == (int)gridDim.x - 1) {
+        *P.peer.done_counter = 0;
+        __threadfence_system();
+        for (int q = 0; q < P.peer.n_peers; ++q)
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.peer.flags[q] + P.peer.rank), "r"(P.peer.step) : "memory");
+      }
+    }
+  }
+}
+
+// One warp: lane r spins on this rank's arrival flag of rank r until it reaches `step` (acquire, system scope).
+// A bounded spin (~4 s of globaltimer) reports through *status instead of hanging the device.
+__global__ void k_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, int* status) {
+  const int r = threadIdx.x;
+  if (r >= n_peers) return;
+  unsigned long long t0, t1;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + r) : "memory");
+    if ((int32_t)(v - step) >= 0) break;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+    if (t1 - t0 > 4000000000ull) { if (status) atomicOr(status, 1 << 8); break; }
+    __nanosleep(200);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1021,8 +1063,14 @@ static int resolve_cap(int A, int nc, int multi_label, int cand_cap) {
 
 static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_thres, int agnostic, int max_nms,
                       int max_det, const int* classes, int n_classes, void* workspace, size_t workspace_bytes,
-                      float* out, int* counts, int* overflow, cudaStream_t s) {
+                      float* out, int* counts, int* overflow, cudaStream_t s, const yb_peer_gather* peer = nullptr) {
   const int B = F.B, A = F.A;
+  if (peer) {
+    YB_CHECK_ARG(peer->n_peers > 0 && peer->n_peers <= YB_MAX_PEERS && peer->rank >= 0 && peer->rank < peer->n_peers &&
+                 peer->done_counter && peer->step > 0, "nms: bad peer-gather table");
+    for (int q = 0; q < peer->n_peers; ++q)
+      YB_CHECK_ARG(peer->out[q] && peer->counts[q] && peer->flags[q], "nms: peer %d has a NULL buffer", q);
+  }
   YB_CHECK_ARG(B > 0 && A > 0 && F.no > 5, "nms: need no >= 6 (nc >= 1)");
   YB_CHECK_ARG(F.no <= 256, "nms: no > 256 unsupported");
   YB_CHECK_ARG(max_det > 0 && max_det <= 4096, "nms: max_det must be in [1,4096]");
@@ -1158,6 +1206,8 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
   if ((double)T > iou_thres) T = nextafterf(T, -INFINITY);
   N.thr_f = T; N.thr_nonneg = (T >= 0.0f) ? 1 : 0;
   N.out = out; N.counts_out = counts;
+  N.has_peer = peer ? 1 : 0;
+  if (peer) N.peer = *peer; else memset(&N.peer, 0, sizeof(N.peer));
   size_t sm_nms = (size_t)max_det * 6 * 4 + (size_t)kChunk * (5 + 4 + 2) * 4 + (size_t)kChunk * kChunkWords * 4 + kChunk;
   // More images than SMs: 512-thread CTAs with 3072-key bands fit two per SM, so the whole batch is resident at once
   // and one CTA's serial phases hide behind the other's; otherwise one 1024-thread CTA per image.
@@ -1202,10 +1252,10 @@ extern "C" int yb_nms(const float* pred, int B, int A, int no, float conf_thres,
                     workspace_bytes, out, counts, overflow, (cudaStream_t)stream);
 }
 
-extern "C" int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no, float conf_thres,
-                             double iou_thres, const int* classes, int n_classes, int agnostic, int multi_label,
-                             int max_nms, int max_det, int cand_cap, void* workspace, size_t workspace_bytes,
-                             float* out, int* counts, int* overflow, void* stream) {
+extern "C" int yb_decode_nms_gather(const yb_head_level* levels, int nl, int na, int no, float conf_thres,
+                                    double iou_thres, const int* classes, int n_classes, int agnostic, int multi_label,
+                                    int max_nms, int max_det, int cand_cap, void* workspace, size_t workspace_bytes,
+                                    float* out, int* counts, int* overflow, const yb_peer_gather* peer, void* stream) {
   YB_CHECK_ARG(levels && nl > 0 && nl <= YB_MAX_LEVELS && na > 0 && na <= YB_MAX_ANCHORS, "yb_decode_nms: bad levels");
   FilterParams F;
   memset(&F, 0, sizeof(F));
@@ -1230,5 +1280,57 @@ extern "C" int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no
   F.multi_label = (multi_label && F.nc > 1) ? 1 : 0;
   F.cap = resolve_cap(A, F.nc, F.multi_label, cand_cap);
   return nms_common(F, true, dt, iou_thres, agnostic, max_nms, max_det, classes, n_classes, workspace,
-                    workspace_bytes, out, counts, overflow, (cudaStream_t)stream);
+                    workspace_bytes, out, counts, overflow, (cudaStream_t)stream, peer);
+}
+
+extern "C" int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no, float conf_thres,
+                             double iou_thres, const int* classes, int n_classes, int agnostic, int multi_label,
+                             int max_nms, int max_det, int cand_cap, void* workspace, size_t workspace_bytes,
+                             float* out, int* counts, int* overflow, void* stream) {
+  return yb_decode_nms_gather(levels, nl, na, no, conf_thres, iou_thres, classes, n_classes, agnostic, multi_label, max_nms,
+                              max_det, cand_cap, workspace, workspace_bytes, out, counts, overflow, nullptr, stream);
+}
+
+extern "C" int yb_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, int* status, void* stream) {
+  YB_CHECK_ARG(flags && n_peers > 0 && n_peers <= YB_MAX_PEERS && n_peers <= 32, "yb_peer_wait: bad arguments");
+  k_peer_wait<<<1, 32, 0, (cudaStream_t)stream>>>(flags, n_peers, step, status);
+  YB_LAUNCH_CHECK();
+  return YB_OK;
+}
+
+// ---- peer memory: one cudaMalloc'd region per rank, shared with the other ranks of the box through CUDA IPC
+extern "C" int yb_peer_alloc(size_t bytes, void** ptr, unsigned char handle[64]) {
+  YB_CHECK_ARG(bytes > 0 && ptr && handle, "yb_peer_alloc: bad arguments");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  YB_CUDA(cudaMalloc(&p, bytes));
+  YB_CUDA(cudaMemset(p, 0, bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    set_error("cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+    return YB_ERR_CUDA;
+  }
+  memcpy(handle, &h, 64);
+  *ptr = p;
+  return YB_OK;
+}
+
+extern "C" int yb_peer_open(const unsigned char handle[64], void** ptr) {
+  YB_CHECK_ARG(handle && ptr, "yb_peer_open: bad arguments");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, 64);
+  YB_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return YB_OK;
+}
+
+extern "C" int yb_peer_close(void* ptr) {
+  if (ptr) YB_CUDA(cudaIpcCloseMemHandle(ptr));
+  return YB_OK;
+}
+
+extern "C" int yb_peer_free(void* ptr) {
+  if (ptr) YB_CUDA(cudaFree(ptr));
+  return YB_OK;
 }

@@ -44,3 +44,122 @@ def gather_detections(out, counts, group=None):
 def to_list(out, counts):
     c = counts.tolist()
     return [out[i, :c[i]] for i in range(out.shape[0])]
+
+
+class PeerGather:
+    """The gather of SURVEY.md 8(e) fused into the NMS kernel (``yb_decode_nms_gather``): every rank owns one
+    cudaMalloc'd region, exported to the other ranks of the box through CUDA IPC, holding two buffer sets of
+    ``(world, B, max_det, 6)`` fp32 detections + ``(world, B)`` int32 counts + ``(world,)`` arrival flags.  The NMS
+    kernel of rank r stores each kept row into block r of EVERY rank's current set over NVLink and raises flag r there;
+    ``finish`` polls the local flags (``yb_peer_wait``) and copies the set out.  Protocol for slot reuse: set
+    ``step & 1`` is written at step s and again at s + 2; a rank can only start step s + 2 after its own ``finish(s + 1)``,
+    which needs every peer's flag for s + 1, which each peer raises after its own ``finish(s)`` copy -- all on the
+    compute stream, so nobody overwrites a set that is still being read.
+    """
+
+    def __init__(self, B, max_det, group=None, device=None):
+        import ctypes as C
+
+        from . import _lib
+        if not (dist.is_available() and dist.is_initialized()):
+            raise RuntimeError('PeerGather needs an initialised torch.distributed process group')
+        self.group = group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > _lib.MAX_PEERS:
+            raise ValueError(f'PeerGather supports up to {_lib.MAX_PEERS} GPUs of one box')
+        self.B, self.max_det = int(B), int(max_det)
+        self.device = device if device is not None else torch.device('cuda', torch.cuda.current_device())
+        self.lib = _lib.lib()
+        w = self.world
+        self.out_floats = w * self.B * self.max_det * 6
+        self.cnt_ints = w * self.B
+        # region layout (bytes): [set0 out | set1 out | set0 counts | set1 counts | set0 flags | set1 flags | done counter]
+        al = lambda n: (n + 255) // 256 * 256
+        self.off_out = [0, al(self.out_floats * 4)]
+        base = 2 * al(self.out_floats * 4)
+        self.off_cnt = [base, base + al(self.cnt_ints * 4)]
+        base += 2 * al(self.cnt_ints * 4)
+        self.off_flag = [base, base + 256]
+        self.off_done = base + 512
+        self.bytes = base + 768
+        ptr, handle = C.c_void_p(), C.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.yb_peer_alloc(self.bytes, C.byref(ptr), handle), 'yb_peer_alloc')
+        self.local = ptr.value
+        handles = [None] * w
+        dist.all_gather_object(handles, handle.raw, group=group)
+        self.peers = []
+        for r in range(w):
+            if r == self.rank:
+                self.peers.append(self.local)
+                continue
+            p = C.c_void_p()
+            with torch.cuda.device(self.device):
+                _lib.check(self.lib.yb_peer_open(handles[r], C.byref(p)), f'yb_peer_open(rank {r})')
+            self.peers.append(p.value)
+        dist.barrier(group=group)          # every region is mapped (and zeroed) before anyone writes a flag
+        self.step = 0
+        self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._views = [self._view_set(s) for s in (0, 1)]
+
+    def _wrap(self, addr, shape, typestr, dtype):
+        class _Cai:
+            pass
+        o = _Cai()
+        o.__cuda_array_interface__ = {'shape': tuple(shape), 'typestr': typestr, 'data': (int(addr), False), 'version': 2}
+        t = torch.as_tensor(o, device=self.device)
+        assert t.dtype == dtype and t.data_ptr() == addr
+        return t
+
+    def _view_set(self, s):
+        w = self.world
+        out = self._wrap(self.local + self.off_out[s], (w * self.B, self.max_det, 6), '<f4', torch.float32)
+        cnt = self._wrap(self.local + self.off_cnt[s], (w * self.B,), '<i4', torch.int32)
+        return out, cnt
+
+    def begin(self, B, max_det):
+        """The table for the next NMS launch: (``_lib.PeerGatherC``, slot, step)."""
+        import ctypes as C
+
+        from . import _lib
+        if (B, max_det) != (self.B, self.max_det):
+            raise ValueError(f'PeerGather was built for B={self.B}, max_det={self.max_det}; got {B}, {max_det}')
+        self.step += 1
+        s = self.step & 1
+        t = _lib.PeerGatherC()
+        t.n_peers, t.rank, t.step = self.world, self.rank, self.step
+        for r, base in enumerate(self.peers):
+            t.out[r] = base + self.off_out[s]
+            t.counts[r] = base + self.off_cnt[s]
+            t.flags[r] = base + self.off_flag[s]
+        t.done_counter = self.local + self.off_done
+        return t, s, self.step
+
+    def finish(self, slot, step):
+        """Wait (on the current stream) until every rank's block of set ``slot`` has arrived, then return private copies
+        ``(out_all (world*B, max_det, 6), counts_all (world*B,))`` in global image order."""
+        import ctypes as C
+
+        from . import _lib
+        _lib.check(self.lib.yb_peer_wait(C.c_void_p(self.local + self.off_flag[slot]), self.world, step,
+                                         C.c_void_p(self.status.data_ptr()), _lib.stream_ptr()), 'yb_peer_wait')
+        out, cnt = self._views[slot]
+        return out.clone(), cnt.clone()
+
+    def check(self):
+        """One 4-byte read-back: raises if a wait timed out (a peer never arrived)."""
+        if int(self.status.item()) != 0:
+            raise RuntimeError('PeerGather: timed out waiting for a peer rank')
+
+    def close(self):
+        import ctypes as C
+        if getattr(self, 'peers', None) is None:
+            return
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)      # nobody is still writing into a region that is about to go away
+        for r, p in enumerate(self.peers):
+            if r != self.rank:
+                self.lib.yb_peer_close(C.c_void_p(p))
+        self._views = None
+        self.lib.yb_peer_free(C.c_void_p(self.local))
+        self.peers = None

@@ -345,10 +345,13 @@ class Model(nn.Module):
 
     @torch.no_grad()
     def detect(self, x, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False, multi_label=False,
-               max_det=300, max_nms=30000, packed=False, augment=False):
+               max_det=300, max_nms=30000, packed=False, augment=False, gather=None):
         """Fused fast path: forward + decode + NMS without materialising ``pred`` (yb_decode_nms).
         Returns the same list as ``non_max_suppression(model(x)[0], ...)``; ``packed=True`` returns the device
-        buffers ``(out (B,max_det,6), meta int32 [counts..., overflow])`` with no host synchronisation."""
+        buffers ``(out (B,max_det,6), meta int32 [counts..., overflow])`` with no host synchronisation.
+        ``gather``: a ``dist.PeerGather`` -- image-sharded multi-GPU inference: the NMS kernel stores every kept row into
+        all GPUs' receive buffers over NVLink and the call returns ``(out_all (world*B, max_det, 6), meta_all)`` in
+        global image order (``meta_all`` = the world*B counts followed by this rank's overflow flag)."""
         from .nms import _run_nms
         if augment:      # TTA: the passes share one pred, then the stand-alone NMS (3x the candidates)
             pred = self.forward(x, augment=True)[0]
@@ -357,13 +360,25 @@ class Model(nn.Module):
         eng = self.run_trunk(x)
         lv, head = self.head_levels(eng)
         A = sum(head.na * v.H * v.W for v in eng.head_views)
+        if gather is not None:
+            table, slot, step = gather.begin(eng.B, max_det)
+            out, meta = _run_nms(None, eng.B, A, head.no, conf_thres, iou_thres, classes, agnostic, multi_label, max_nms,
+                                 max_det, eng.device, levels=(lv, head.nl, head.na), return_packed=True, peer=table)
+            out_all, cnt_all = gather.finish(slot, step)
+            meta_all = torch.cat((cnt_all, meta[-1:]))
+            if packed:
+                return out_all, meta_all
+            host = meta_all.cpu()
+            if int(host[-1]) != 0:
+                raise RuntimeError('yb_nms: candidate capacity exceeded (YB_ERR_OVERFLOW)')
+            return [out_all[i, :int(host[i])] for i in range(out_all.shape[0])]
         return _run_nms(None, eng.B, A, head.no, conf_thres, iou_thres, classes, agnostic, multi_label, max_nms,
                         max_det, eng.device, levels=(lv, head.nl, head.na), return_packed=packed)
 
 
     @torch.no_grad()
     def detect_batches(self, batches, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False,
-                       multi_label=False, max_det=300, max_nms=30000, post=None):
+                       multi_label=False, max_det=300, max_nms=30000, post=None, gather=None):
         """Streaming form of ``detect`` for host batches (the detect.py:87-152 loop over a dataset): a generator that
         takes (B, 3, H, W) uint8/float32 HOST tensors (pinned for real overlap) and yields, in order, one
         ``(out (B', max_det, 6) fp32, counts (B',) int32)`` pair of pinned HOST tensors per batch.
@@ -371,7 +386,8 @@ class Model(nn.Module):
         Three streams, two slots: batch i+1's H2D copy and batch i-1's D2H read run on their own copy streams
         while batch i computes on the caller's stream, so PCIe time leaves the critical path; each step still
         moves its own input H2D and its own result D2H.  ``post(out, counts) -> (out, counts)`` runs on the compute
-        stream before the read-back (e.g. ``dist.gather_detections``).  A yielded pair stays valid until the next
+        stream before the read-back (e.g. ``dist.gather_detections``); ``gather`` (a ``dist.PeerGather``) does the multi-GPU
+        exchange inside the NMS kernel instead and every yielded pair then covers the global batch.  A yielded pair stays valid until the next
         batch is drawn (its pinned buffers are reused two batches later)."""
         from collections import deque
         dev = self._device()
@@ -405,7 +421,7 @@ class Model(nn.Module):
                 s['loaded'].record(h2d)
             main.wait_event(s['loaded'])
             out, meta = self.detect(s['stage'], conf_thres, iou_thres, classes, agnostic, multi_label, max_det,
-                                    max_nms, packed=True)
+                                    max_nms, packed=True, gather=gather)
             s['consumed'].record(main)
             ovf = meta[-1:]
             if post is not None:

@@ -14,8 +14,8 @@ from . import _lib
 _ws_cache = {}
 
 
-def _workspace(nbytes, device):
-    key = str(device)
+def _workspace(nbytes, device, slot=0):
+    key = (str(device), slot)
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=device)
@@ -24,7 +24,9 @@ def _workspace(nbytes, device):
 
 
 def _run_nms(pred, B, A, no, conf_thres, iou_thres, classes, agnostic, multi_label, max_nms, max_det, device,
-             levels=None, cand_cap=0, return_packed=False):
+             levels=None, cand_cap=0, return_packed=False, peer=None):
+    """``peer``: a ``_lib.PeerGatherC`` table (dist.PeerGather.table) -- the fused path then also stores every kept row
+    into the receive buffers of all GPUs of the box (yb_decode_nms_gather)."""
     L = _lib.lib()
     nbytes = L.yb_nms_workspace_bytes(B, A, no, int(bool(multi_label)), int(cand_cap))
     ws = _workspace(nbytes, device)
@@ -39,13 +41,18 @@ def _run_nms(pred, B, A, no, conf_thres, iou_thres, classes, agnostic, multi_lab
     ws_len = ws.numel() - (ws_ptr - ws.data_ptr())
     common = (C.c_float(conf_thres), C.c_double(iou_thres), cls_arr, n_cls, int(bool(agnostic)),
               int(bool(multi_label)), int(max_nms), int(max_det), int(cand_cap), C.c_void_p(ws_ptr), ws_len,
-              C.c_void_p(out.data_ptr()), C.c_void_p(meta.data_ptr()), C.c_void_p(meta.data_ptr() + 4 * B),
-              _lib.stream_ptr())
+              C.c_void_p(out.data_ptr()), C.c_void_p(meta.data_ptr()), C.c_void_p(meta.data_ptr() + 4 * B))
     if levels is None:
-        _lib.check(L.yb_nms(C.c_void_p(pred.data_ptr()), B, A, no, *common), 'yb_nms')
+        if peer is not None:
+            raise ValueError('the peer gather is fused into yb_decode_nms_gather (Model.detect), not the stand-alone yb_nms')
+        _lib.check(L.yb_nms(C.c_void_p(pred.data_ptr()), B, A, no, *common, _lib.stream_ptr()), 'yb_nms')
+    elif peer is not None:
+        lv, nl, na = levels
+        _lib.check(L.yb_decode_nms_gather(lv, nl, na, no, *common, C.byref(peer), _lib.stream_ptr()),
+                   'yb_decode_nms_gather')
     else:
         lv, nl, na = levels
-        _lib.check(L.yb_decode_nms(lv, nl, na, no, *common), 'yb_decode_nms')
+        _lib.check(L.yb_decode_nms(lv, nl, na, no, *common, _lib.stream_ptr()), 'yb_decode_nms')
     if return_packed:
         return out, meta
     host = meta.cpu()   # the single device->host read of the call (B+1 ints)
