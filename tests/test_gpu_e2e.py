@@ -134,3 +134,43 @@ def test_detect_batches_stream_equals_detect():
             assert torch.equal(o[i, :c[i]], wo[i, :c[i]])
     assert sum(int(c.sum()) for _, c in got) > 0
     assert list(m.detect_batches(iter([]), 0.05, 0.5)) == []
+
+
+def test_peer_gather_single_rank_equals_detect():
+    """The gather fused into the NMS kernel (yb_decode_nms_gather + yb_peer_wait, dist.PeerGather) on a one-rank group:
+    rows go through the peer-store path into the (self-mapped) receive buffer, both buffer sets are exercised and the
+    result equals the plain fused path bit for bit.  (2 and 8 GPUs: scripts/check_dist_gpu.py, profiles/round1_dist_check.txt.)"""
+    import os
+    import socket
+
+    import torch.distributed as dist
+
+    from yolo_series_b200 import dist as ydist
+    if dist.is_initialized():
+        pytest.skip('a process group already exists in this process')
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    os.environ['MASTER_ADDR'], os.environ['MASTER_PORT'] = '127.0.0.1', str(port)
+    dist.init_process_group('gloo', rank=0, world_size=1)
+    try:
+        m = _build('yolov7-tiny', 'bf16')
+        x = synth_image(4, 96, 128, seed=8, dtype=torch.uint8).cuda()
+        want_out, want_meta = m.detect(x, 0.05, 0.5, max_det=50, packed=True)
+        pg = ydist.PeerGather(4, 50)
+        for _ in range(3):
+            out, meta = m.detect(x, 0.05, 0.5, max_det=50, packed=True, gather=pg)
+            assert torch.equal(meta, want_meta)
+            for i in range(4):
+                n = int(meta[i])
+                assert torch.equal(out[i, :n], want_out[i, :n])
+        lst = m.detect(x, 0.05, 0.5, max_det=50, gather=pg)
+        assert [d.shape[0] for d in lst] == want_meta[:4].tolist()
+        pg.check()
+        with pytest.raises(ValueError):
+            pg.begin(8, 50)
+        pg.close()
+        assert int(want_meta[:4].sum()) > 0
+    finally:
+        dist.destroy_process_group()
