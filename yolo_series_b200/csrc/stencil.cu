@@ -126,12 +126,13 @@ __global__ void __launch_bounds__(256) k_pool_s1(yb_tensor x, yb_tensor y, int k
   }
 }
 
-// ---- fused SPP: one CTA = one image x 128-byte channel group; plane staged in shared memory.
+// ---- fused SPP: one CTA = one image x (VPP x 16)-byte channel group; plane staged in shared memory.
 // pass(src)->dst is a separable 5-tap max (rows then columns); m5 = pass(x), m9 = pass(m5), m13 = pass(m9).
-template <typename T>
-__global__ void __launch_bounds__(256) k_spp3(yb_tensor x, yb_tensor y5, yb_tensor y9, yb_tensor y13) {
+// VPP = 2 (32-byte sectors) keeps a CTA's plane small (many CTAs per SM, many CTAs even at batch 1: the kernel is
+// seven dependent phases, i.e. latency bound per CTA); pixel -> (h, w) by multiplication (magic_w = 2^32 / W + 1).
+template <typename T, int VPP>
+__global__ void __launch_bounds__(256) k_spp3(yb_tensor x, yb_tensor y5, yb_tensor y9, yb_tensor y13, unsigned magic_w) {
   using V = Vec16<T>;
-  constexpr int VPP = 8;  // 16-byte vectors per pixel per CTA (128 B)
   extern __shared__ __align__(16) uint4 smem[];
   const int H = x.H, W = x.W, HW = H * W;
   uint4* A = smem;
@@ -142,15 +143,17 @@ __global__ void __launch_bounds__(256) k_spp3(yb_tensor x, yb_tensor y5, yb_tens
   const int nv = min(VPP, x.C / V::N - cv0);
   const int items = HW * VPP;
   for (int i = threadIdx.x; i < items; i += blockDim.x) {
-    int v = i % VPP, p = i / VPP;
-    if (v < nv) A[i] = __ldg(vptr<T>(x, n, p / W, p % W, cv0 + v));
+    const int v = i % VPP, p = i / VPP;
+    const int h = magic_w ? (int)__umulhi((unsigned)p, magic_w) : p, w = p - h * W;
+    if (v < nv) A[i] = __ldg(vptr<T>(x, n, h, w, cv0 + v));
   }
   __syncthreads();
   yb_tensor outs[3] = {y5, y9, y13};
 #pragma unroll 1
   for (int pass = 0; pass < 3; ++pass) {
     for (int i = threadIdx.x; i < items; i += blockDim.x) {  // horizontal: A -> Bf
-      int v = i % VPP, p = i / VPP, w = p % W;
+      const int v = i % VPP, p = i / VPP;
+      const int h = magic_w ? (int)__umulhi((unsigned)p, magic_w) : p, w = p - h * W;
       if (v >= nv) continue;
       uint4 m = A[i];
 #pragma unroll
@@ -162,7 +165,8 @@ __global__ void __launch_bounds__(256) k_spp3(yb_tensor x, yb_tensor y5, yb_tens
     }
     __syncthreads();
     for (int i = threadIdx.x; i < items; i += blockDim.x) {  // vertical: Bf -> A (+ global)
-      int v = i % VPP, p = i / VPP, h = p / W;
+      const int v = i % VPP, p = i / VPP;
+      const int h = magic_w ? (int)__umulhi((unsigned)p, magic_w) : p, w = p - h * W;
       if (v >= nv) continue;
       uint4 m = Bf[i];
 #pragma unroll
@@ -171,7 +175,7 @@ __global__ void __launch_bounds__(256) k_spp3(yb_tensor x, yb_tensor y5, yb_tens
         if (h + d < H) m = V::vmax(m, Bf[i + d * W * VPP]);
       }
       A[i] = m;
-      *vptr_w<T>(outs[pass], n, h, p % W, cv0 + v) = m;
+      *vptr_w<T>(outs[pass], n, h, w, cv0 + v) = m;
     }
     __syncthreads();
   }
@@ -287,17 +291,20 @@ extern "C" int yb_spp3(const yb_tensor* x, const yb_tensor* y5, const yb_tensor*
   if (rc) return rc;
   YB_CHECK_ARG(y5->H == x->H && y5->W == x->W && y9->H == x->H && y9->W == x->W && y13->H == x->H && y13->W == x->W,
                "yb_spp3: shape mismatch");
-  const size_t smem = (size_t)x->H * x->W * 128 * 2;
-  if (smem > 200 * 1024) {  // plane does not fit: three generic passes (rect / huge inputs)
+  constexpr int kSppVpp = 2;
+  const size_t smem = (size_t)x->H * x->W * kSppVpp * 16 * 2;
+  if (smem > 200 * 1024 || (long long)x->H * x->W * x->W >= 0x100000000LL) {  // plane does not fit: three generic passes
     if ((rc = yb_maxpool_s1(x, y5, 5, stream))) return rc;
     if ((rc = yb_maxpool_s1(x, y9, 9, stream))) return rc;
     return yb_maxpool_s1(x, y13, 13, stream);
   }
   const int vn = x->dtype == YB_F32 ? 4 : 8;
-  const int groups = ceil_div(x->C / vn, 8);
+  const int groups = ceil_div(x->C / vn, kSppVpp);
+  const unsigned magic_w = x->W > 1 ? (unsigned)(0x100000000ULL / (unsigned long long)x->W) + 1u : 0u;
   YB_DISPATCH_T(x->dtype, {
-    YB_CUDA(cudaFuncSetAttribute(k_spp3<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_spp3<T><<<x->N * groups, 256, smem, (cudaStream_t)stream>>>(*x, *y5, *y9, *y13);
+    if (smem > 48 * 1024)
+      YB_CUDA(cudaFuncSetAttribute(k_spp3<T, kSppVpp>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_spp3<T, kSppVpp><<<x->N * groups, 256, smem, (cudaStream_t)stream>>>(*x, *y5, *y9, *y13, magic_w);
   });
   YB_LAUNCH_CHECK();
   return YB_OK;
