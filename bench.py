@@ -219,7 +219,14 @@ def main():
     # N > 1: the one exchange of the path (every rank's detections to every rank) happens inside the NMS kernel through
     # peer-to-peer stores over NVLink (dist.PeerGather); YB_GATHER=nccl selects the plain NCCL all-gather instead.
     use_peer = world > 1 and os.environ.get('YB_GATHER', 'peer') != 'nccl'
-    pg = ydist.PeerGather(B, MAX_DET, device=dev) if use_peer else None
+    pg = None
+    if use_peer:
+        try:
+            pg = ydist.PeerGather(B, MAX_DET, device=dev)
+        except RuntimeError as ex:          # raised on every rank together: CUDA IPC unavailable -> NCCL all-gather
+            use_peer = False
+            if rank == 0:
+                print(f'[bench] {ex}', file=sys.stderr)
 
     def step_device():
         out, meta = model.detect(x_dev, CONF, IOU, max_det=MAX_DET, packed=True, gather=pg)

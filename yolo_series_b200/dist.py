@@ -82,22 +82,42 @@ class PeerGather:
         self.off_flag = [base, base + 256]
         self.off_done = base + 512
         self.bytes = base + 768
-        ptr, handle = C.c_void_p(), C.create_string_buffer(64)
-        with torch.cuda.device(self.device):
-            _lib.check(self.lib.yb_peer_alloc(self.bytes, C.byref(ptr), handle), 'yb_peer_alloc')
+        # Every rank must reach the same verdict (a rank that failed alone would leave the others in a barrier), so the
+        # outcome of each stage is agreed on through all_gather_object before anyone proceeds.
+        ptr, handle, err = C.c_void_p(), C.create_string_buffer(64), None
+        try:
+            with torch.cuda.device(self.device):
+                _lib.check(self.lib.yb_peer_alloc(self.bytes, C.byref(ptr), handle), 'yb_peer_alloc')
+        except RuntimeError as ex:
+            err = str(ex)
         self.local = ptr.value
         handles = [None] * w
-        dist.all_gather_object(handles, handle.raw, group=group)
+        dist.all_gather_object(handles, (handle.raw, err), group=group)
         self.peers = []
-        for r in range(w):
-            if r == self.rank:
-                self.peers.append(self.local)
-                continue
-            p = C.c_void_p()
-            with torch.cuda.device(self.device):
-                _lib.check(self.lib.yb_peer_open(handles[r], C.byref(p)), f'yb_peer_open(rank {r})')
-            self.peers.append(p.value)
-        dist.barrier(group=group)          # every region is mapped (and zeroed) before anyone writes a flag
+        if all(h[1] is None for h in handles):
+            for r in range(w):
+                if r == self.rank:
+                    self.peers.append(self.local)
+                    continue
+                p = C.c_void_p()
+                try:
+                    with torch.cuda.device(self.device):
+                        _lib.check(self.lib.yb_peer_open(handles[r][0], C.byref(p)), f'yb_peer_open(rank {r})')
+                except RuntimeError as ex:
+                    err = str(ex)
+                    break
+                self.peers.append(p.value)
+        verdicts = [None] * w
+        dist.all_gather_object(verdicts, err or next((h[1] for h in handles if h[1]), None), group=group)
+        bad = next((v for v in verdicts if v), None)
+        if bad:                                # same decision on every rank
+            for r, p in enumerate(self.peers):
+                if r != self.rank:
+                    self.lib.yb_peer_close(C.c_void_p(p))
+            if self.local:
+                self.lib.yb_peer_free(C.c_void_p(self.local))
+            self.peers = None
+            raise RuntimeError(f'PeerGather: peer memory is not available on this box ({bad}); use dist.gather_detections')
         self.step = 0
         self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._views = [self._view_set(s) for s in (0, 1)]
