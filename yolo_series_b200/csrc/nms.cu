@@ -584,6 +584,7 @@ struct NmsParams {
   float* out;            // [B][max_det][6]
   int* counts_out;       // [B]
   int band_cap;          // keys per band (<= kBandCap): sized with the shared memory of the launch
+  unsigned long long* dbg;
   int has_peer;          // yb_decode_nms_gather: detections also go straight into every peer's receive buffer
   yb_peer_gather peer;
 };
@@ -603,6 +604,11 @@ __device__ __forceinline__ bool iou_suppresses(float ix1, float iy1, float ix2, 
 // (at least kBandMin keys, at most kBandCap so that it sorts inside shared memory), sorted, and fed to the greedy
 // loop, which usually reaches max_det inside the first band.  Bands are disjoint key ranges taken in key order and
 // every key is distinct, so the sequence of candidates is exactly that of one full sort (general.py:695-699).
+#ifdef YB_NMS_TIMING
+#define YB_TS(slot) do { if (threadIdx.x == 0 && (slot) < 64) { unsigned long long t_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_)); P.dbg[blockIdx.x * 64 + (slot)] = t_; } } while (0)
+#else
+#define YB_TS(slot) do { } while (0)
+#endif
 constexpr int kBuckets = 128;            // class buckets of the kept set (k_sort_nms)
 constexpr float kBucketExtent = 4000.0f; // < kMaxWH with room for the rounding of x + cls * 4096
 __device__ __forceinline__ int ordered_int(float f) { const int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
@@ -827,7 +833,9 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
     if (!have_lo && n <= band_cap) {
       band_n = n;
     } else {
+      YB_TS(0);
       select_band(gkeys, n, lo, have_lo, scratch, s_sel, band_cap);
+      YB_TS(1);
       band_n = (int)s_sel[0];
       T = s_sel[1];
     }
@@ -856,13 +864,16 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
         if (sel) band_a[pos] = key;
       }
       __syncthreads();
+      YB_TS(2);
       src = block_radix_sort(band_a, band_b, band_n, scratch);
+      YB_TS(3);
       lo = T;
       have_lo = true;
     }
     const int m = min(band_n, m_total - consumed);
 
   for (int base = 0; base < m; base += kChunk) {
+    YB_TS(4 + base / kChunk);
     const int K = s_K;
     if (K >= P.max_det) break;
     const int cnt = min(kChunk, m - base);
@@ -897,6 +908,7 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
     if (tid == 0 && s_bucket_ok && !(__fsub_rn(ordered_float(s_xmax), ordered_float(s_xmin)) <= kBucketExtent)) s_bucket_ok = 0;
     __syncthreads();
     const bool bucket_mode = s_bucket_ok != 0;
+    if (base == 0) YB_TS(50);
     // ---- phase A: candidate j vs every kept box (parts = blockDim / kChunk = 4 or 2 threads per candidate)
     {
       const int j = tid >> pshift, part = tid & (parts - 1);
@@ -925,55 +937,80 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       if (part == 0) calive[j] = (j < cnt && !s) ? 1 : 0;
     }
     __syncthreads();
+    if (base == 0) YB_TS(51);
     if (tid < kChunkWords) {
       uint32_t w = 0;
       for (int q = 0; q < 32; ++q) w |= (uint32_t)calive[tid * 32 + q] << q;
       s_alive[tid] = w;
       s_new[tid] = 0;
     }
-    // ---- phase B: intra-chunk suppression bit matrix, rows of live candidates only
+    // ---- phase B: intra-chunk suppression bit matrix, rows of live candidates only.  A warp owns a row i; lane q tests
+    // candidate j = w*32 + q of word w (its box comes from consecutive shared-memory words, row i's box is uniform) and the
+    // warp ballot IS the matrix word.  Only words that hold some j > i are produced (phase C reads nothing else).
     {
-      const int i = tid >> pshift, part = tid & (parts - 1);
-      if (i < cnt && calive[i]) {
+      const int warp = tid >> 5, nwarps = (int)blockDim.x >> 5;
+      for (int i = warp; i < cnt; i += nwarps) {
+        if (!calive[i]) continue;
         const float ix1 = cx1[i], iy1 = cy1[i], ix2 = cx2[i], iy2 = cy2[i], ia = car[i], ci = ccls[i];
-        for (int w = part; w < kChunkWords; w += parts) {
-          uint32_t word = 0;
-          const int j0 = w * 32;
-          if (j0 + 31 > i) {
-            for (int q = 0; q < 32; ++q) {
-              const int j = j0 + q;
-              if (j > i && j < cnt && calive[j] && (!bucket_mode || ccls[j] == ci) &&
-                  iou_suppresses(ix1, iy1, ix2, iy2, ia, cx1[j], cy1[j], cx2[j], cy2[j], car[j], P.thr_f, P.thr_nonneg))
-                word |= 1u << q;
-            }
-          }
-          cmask[i * kChunkWords + w] = word;
+        for (int w = i >> 5; w < kChunkWords; ++w) {
+          const int j = w * 32 + lane;
+          bool sup = false;
+          if (j > i && j < cnt && calive[j] && (!bucket_mode || ccls[j] == ci))
+            sup = iou_suppresses(ix1, iy1, ix2, iy2, ia, cx1[j], cy1[j], cx2[j], cy2[j], car[j], P.thr_f, P.thr_nonneg);
+          const uint32_t word = __ballot_sync(0xffffffffu, sup);
+          if (lane == 0) cmask[i * kChunkWords + w] = word;
         }
       }
     }
     __syncthreads();
-    // ---- phase C: serial resolve over live candidates (one thread; cost ~ number kept)
-    if (tid == 0) {
+    if (base == 0) YB_TS(52);
+    // ---- phase C: resolve the chunk in order, warp 0 cooperatively, one 32-candidate word at a time.  Lane q holds row
+    // (w*32 + q) of the bit matrix.  If no candidate of the word suppresses another one, all of them are kept at once;
+    // otherwise the greedy order is walked with ffs + one shuffle per kept box (no shared-memory round trip on the
+    // dependent chain).  The rows of the boxes kept in the word are OR-reduced across the warp into the removed masks
+    // of the later words.
+    if (tid < 32) {
       uint32_t removed[kChunkWords];
 #pragma unroll
       for (int w = 0; w < kChunkWords; ++w) removed[w] = 0;
       int Kc = K;
-#pragma unroll 1
-      for (int w = 0; w < kChunkWords && Kc < P.max_det; ++w) {
-        uint32_t bits = s_alive[w] & ~removed[w];
-        while (bits && Kc < P.max_det) {
-          const int q = __ffs(bits) - 1;
-          const int i = w * 32 + q;
-          s_new[w] |= 1u << q;
-          ++Kc;
 #pragma unroll
-          for (int ww = 0; ww < kChunkWords; ++ww) removed[ww] |= cmask[i * kChunkWords + ww];
-          bits = s_alive[w] & ~removed[w] & ~((2u << q) - 1u);
+      for (int w = 0; w < kChunkWords; ++w) {
+        const uint32_t alive_w = s_alive[w];
+        uint32_t rowv[kChunkWords];
+        const bool live = (alive_w >> lane) & 1u;            // rows of dead candidates were never written
+#pragma unroll
+        for (int ww = 0; ww < kChunkWords; ++ww) rowv[ww] = (live && ww >= w) ? cmask[(w * 32 + lane) * kChunkWords + ww] : 0u;
+        const uint32_t cand = alive_w & ~removed[w];
+        const int room = P.max_det - Kc;
+        uint32_t kept = 0;
+        if (cand && room > 0) {
+          const bool cq = (cand >> lane) & 1u;
+          if (!__any_sync(0xffffffffu, cq && (rowv[w] & cand)) && __popc(cand) <= room) {
+            kept = cand;
+          } else {
+            uint32_t rem = cand;
+            int left = room;
+            while (rem && left > 0) {
+              const int q = __ffs(rem) - 1;
+              kept |= 1u << q;
+              --left;
+              const uint32_t sup = __shfl_sync(0xffffffffu, rowv[w], q);
+              rem &= ~sup & ~((2u << q) - 1u);
+            }
+          }
+          Kc += __popc(kept);
         }
+        if (lane == 0) s_new[w] = kept;
+        const bool mine = (kept >> lane) & 1u;
+#pragma unroll
+        for (int ww = 0; ww < kChunkWords; ++ww)
+          if (ww > w) removed[ww] |= __reduce_or_sync(0xffffffffu, mine ? rowv[ww] : 0u);
       }
-      s_K = Kc;
+      if (lane == 0) s_K = Kc;
     }
     __syncthreads();
+    if (base == 0) YB_TS(53);
     // ---- phase D: append the newly kept boxes to the kept set and write output rows
     if (tid < cnt && ((s_new[tid >> 5] >> (tid & 31)) & 1u)) {
       int pos = K + __popc(s_new[tid >> 5] & ((1u << (tid & 31)) - 1u));
@@ -997,6 +1034,7 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
     }
     __syncthreads();
   }
+    YB_TS(40);
     consumed += band_n;
   }
   if (tid == 0) P.counts_out[b] = s_K;
@@ -1206,6 +1244,7 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
   if ((double)T > iou_thres) T = nextafterf(T, -INFINITY);
   N.thr_f = T; N.thr_nonneg = (T >= 0.0f) ? 1 : 0;
   N.out = out; N.counts_out = counts;
+  N.dbg = reinterpret_cast<unsigned long long*>(W.keys_b);
   N.has_peer = peer ? 1 : 0;
   if (peer) N.peer = *peer; else memset(&N.peer, 0, sizeof(N.peer));
   size_t sm_nms = (size_t)max_det * 6 * 4 + (size_t)kChunk * (5 + 4 + 2) * 4 + (size_t)kChunk * kChunkWords * 4 + kChunk;
