@@ -25,6 +25,7 @@ struct HeadLevelDev {  // fused decode source (yb_decode_nms)
   float anchor_wh[2 * YB_MAX_ANCHORS];
   int row_off;
   unsigned magic_cells, magic_nx;   // floor(2^32 / d) + 1 for d = ny*nx and d = nx
+  unsigned magic_cs;                // same for d = c_stride (k_filter_cells staging)
   int blk_off;                      // k_filter_cells: first block (within an image) of this level
 };
 
@@ -225,11 +226,27 @@ __device__ __forceinline__ bool fb_process_row(const FilterParams& P, const floa
       float s_lo = sigmoid_rn_(cut);
       s_lo = __uint_as_float(__float_as_uint(s_lo) + 8u);            // eight ulps up (s_lo >= 0)
       const bool margin_ok = __fmul_rn(s_lo, obj) < conf_M;          // NaN logits fail the test -> full scan
-#pragma unroll 8
-      for (int c = 0; c < P.nc; ++c) {
+      // classes below the gate cannot reach the maximum: four of them are dismissed with one branch
+      const float gate = margin_ok ? cut : -INFINITY;
+      int c = 0;
+#pragma unroll 2
+      for (; c + 4 <= P.nc; c += 4) {
+        const float v0 = r[5 + c], v1 = r[6 + c], v2 = r[7 + c], v3 = r[8 + c];
+        if (!(v0 < gate) || !(v1 < gate) || !(v2 < gate) || !(v3 < gate)) {
+          const float v[4] = {v0, v1, v2, v3};
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (!(v[u] < gate)) {
+              const float conf = v[u] == M ? conf_M : __fmul_rn(sigmoid_rn_(v[u]), obj);   // same logit, same product
+              if (conf > best) { best = conf; best_c = c + u; }
+            }
+          }
+        }
+      }
+      for (; c < P.nc; ++c) {
         const float lc = r[5 + c];
-        if (margin_ok && lc < cut) continue;
-        const float conf = lc == M ? conf_M : __fmul_rn(sigmoid_rn_(lc), obj);   // same logit, same product
+        if (lc < gate) continue;
+        const float conf = lc == M ? conf_M : __fmul_rn(sigmoid_rn_(lc), obj);
         if (conf > best) { best = conf; best_c = c; }
       }
     }
@@ -523,9 +540,16 @@ __global__ void __launch_bounds__(kFbThreads) k_filter_cells(const FilterParams 
         const int i = i0 + u * kFbThreads + tid;
         if (i < nvec) {
           const int e = 4 * i;
-          const int cell = e / L.c_stride, off = e - cell * L.c_stride;   // c_stride % 4 == 0: one cell per vector
+          // c_stride % 4 == 0: one cell per vector; e / c_stride by multiplication (e * c_stride < 2^32)
+          const int cell = L.magic_cs ? (int)__umulhi((unsigned)e, L.magic_cs) : e, off = e - cell * L.c_stride;
           float* d = tile + cell * pitch + off;
-          d[0] = v[u].x; d[1] = v[u].y; d[2] = v[u].z; d[3] = v[u].w;
+          // lanes l, l+8, l+16, l+24 sit 32 words apart: each group of eight lanes stores its four values in an order
+          // rotated by lane/8, so that the four store instructions are bank-conflict free
+          const int rr = lane >> 3;
+          float a0 = v[u].x, a1 = v[u].y, a2 = v[u].z, a3 = v[u].w;
+          if (rr & 1) { const float t0 = a0; a0 = a1; a1 = a2; a2 = a3; a3 = t0; }
+          if (rr & 2) { const float t0 = a0, t1 = a1; a0 = a2; a1 = a3; a2 = t0; a3 = t1; }
+          d[rr & 3] = a0; d[(rr + 1) & 3] = a1; d[(rr + 2) & 3] = a2; d[(rr + 3) & 3] = a3;
         }
       }
     }
@@ -1312,6 +1336,7 @@ extern "C" int yb_decode_nms_gather(const yb_head_level* levels, int nl, int na,
     L.row_off = A;
     L.magic_cells = t.H * t.W > 1 ? (unsigned)(0x100000000ULL / (unsigned long long)(t.H * t.W)) + 1u : 0u;
     L.magic_nx = t.W > 1 ? (unsigned)(0x100000000ULL / (unsigned long long)t.W) + 1u : 0u;
+    L.magic_cs = t.c_stride > 1 ? (unsigned)(0x100000000ULL / (unsigned long long)t.c_stride) + 1u : 0u;
     YB_CHECK_ARG((long long)na * t.H * t.W * t.H * t.W < 0x100000000LL, "yb_decode_nms: level %d too large", l);
     A += na * t.H * t.W;
   }
