@@ -174,3 +174,19 @@ def test_peer_gather_single_rank_equals_detect():
         assert int(want_meta[:4].sum()) > 0
     finally:
         dist.destroy_process_group()
+
+
+def test_accelerate_wrapper_runs_the_engine():
+    """accelerate(model) (the INTEGRATION.md route for checkpoints unpickled by attempt_load) drives the same engine:
+    wrapping a module tree gives bit-identical predictions and detections (the duck-typing against the reference's own
+    classes is pinned on the CPU by tests/test_zoo.py::test_accelerate_lowers_a_real_reference_model)."""
+    from yolo_series_b200 import accelerate, non_max_suppression
+    m = _build('yolov7-tiny', 'bf16')
+    acc = accelerate(m).half()
+    x = synth_image(2, 96, 128, seed=5, dtype=torch.uint8).cuda()
+    p0, r0 = m(x)
+    p1, r1 = acc(x)
+    assert torch.equal(p0, p1) and all(torch.equal(a, b) for a, b in zip(r0, r1))
+    d0, d1 = non_max_suppression(p0, 0.05, 0.5), acc.detect(x, 0.05, 0.5)
+    assert all(torch.equal(a, b) for a, b in zip(d0, d1))
+    assert acc.stride.tolist() == [8., 16., 32.] and next(acc.parameters()).is_cuda
