@@ -353,6 +353,9 @@ class Model(nn.Module):
         all GPUs' receive buffers over NVLink and the call returns ``(out_all (world*B, max_det, 6), meta_all)`` in
         global image order (``meta_all`` = the world*B counts followed by this rank's overflow flag)."""
         from .nms import _run_nms
+        if augment and gather is not None:
+            raise NotImplementedError('detect(augment=True, gather=...): the peer gather is fused into the single-pass '
+                                      'decode+NMS kernel; gather TTA results with dist.gather_detections')
         if augment:      # TTA: the passes share one pred, then the stand-alone NMS (3x the candidates)
             pred = self.forward(x, augment=True)[0]
             return _run_nms(pred, pred.shape[0], pred.shape[1], pred.shape[2], conf_thres, iou_thres, classes, agnostic,
