@@ -60,6 +60,15 @@ def test_config2_yolov7_640_b32_properties():
     ref = non_max_suppression_ref(pred[:2].cpu(), CONF, IOU)
     for i in range(2):
         assert np.array_equal(dets[i].cpu().numpy(), ref[i].numpy())
+    # multi_label=True variant (test.py:126): fused == unfused on the whole batch, oracle on one image
+    om, mm = m.detect(x, CONF, IOU, multi_label=True, packed=True)
+    assert int(mm[-1]) == 0
+    _check_nms_invariants(om, mm[:-1], IOU, 300)
+    dm = non_max_suppression(pred, CONF, IOU, multi_label=True)
+    for i, d in enumerate(dm):
+        assert torch.equal(d, om[i, :int(mm[i])]), i
+    refm = non_max_suppression_ref(pred[5:6].cpu(), CONF, IOU, multi_label=True)[0]
+    assert np.array_equal(dm[5].cpu().numpy(), refm.numpy())
     # bf16 trunk vs the fp32 reference mode on the device (stated bf16 tolerance, tests/test_gpu_e2e.py), 8 images
     m32 = _build('yolov7', 'fp32')
     p32 = m32(x[:8])[0]
