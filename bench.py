@@ -50,7 +50,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(['nvidia-smi', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits',
-                                          '-lms', '100', '-i', str(self.index)], stdout=subprocess.PIPE, text=True)
+                                          '-lms', '50', '-i', str(self.index)], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -58,7 +58,12 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(',')])
+            self.rows.append([time.time()] + [c.strip() for c in line.split(',')])
+
+    def window(self, t0, t1):
+        """Keep the samples taken inside [t0, t1] (the sampler is started before the warm-up so that nvidia-smi's own
+        start-up -- NVML initialisation stalls launches for milliseconds -- does not fall into the timed region)."""
+        self.t0, self.t1 = t0, t1
 
     def stop(self):
         if not self.proc:
@@ -71,7 +76,9 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        for r in self.rows:
+        t0, t1 = getattr(self, 't0', 0.0), getattr(self, 't1', float('inf'))
+        inside = [r[1:] for r in self.rows if t0 <= r[0] <= t1 + 0.12]
+        for r in (inside if inside else [r[1:] for r in self.rows[-3:]]):
             if len(r) < 7:
                 continue
             try:
@@ -247,19 +254,21 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        step_device()
-    barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    t_wall0 = time.time()
     e0.record()
     for _ in range(args.steps):
         out, meta = step_device()
     e1.record()
     barrier()
+    sampler.window(t_wall0, time.time())
     ms_dev = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
     # ---- end-to-end through the public API with host buffers
