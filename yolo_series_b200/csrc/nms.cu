@@ -642,7 +642,9 @@ constexpr int kBandCap = 4096;
 
 // Stable LSD radix sort (8-bit digits) of n 64-bit keys by the whole block; src/dst may be shared or global.
 // Returns the buffer holding the sorted keys.  whist: [kSortWarps][256] ints of scratch.
-__device__ uint64_t* block_radix_sort(uint64_t* src, uint64_t* dst, int n, int* whist) {
+// `consider` masks the key bits that take part (digits outside it are skipped like constant digits).
+__device__ uint64_t* block_radix_sort(uint64_t* src, uint64_t* dst, int n, int* whist,
+                                      unsigned long long consider = ~0ull) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   __shared__ unsigned long long s_and, s_or;
   __shared__ int digit_tot[256];
@@ -658,7 +660,7 @@ __device__ uint64_t* block_radix_sort(uint64_t* src, uint64_t* dst, int n, int* 
   }
   if (lane == 0) { atomicAnd(&s_and, a); atomicOr(&s_or, o); }
   __syncthreads();
-  const unsigned long long varying = s_and ^ s_or;
+  const unsigned long long varying = (s_and ^ s_or) & consider;
   // contiguous segment of the array owned by each warp (keeps the scatter stable)
   const int per_warp = ((n + ((int)blockDim.x >> 5) - 1) / ((int)blockDim.x >> 5) + 31) / 32 * 32;
   const int seg0 = min(n, warp * per_warp), seg1 = min(n, seg0 + per_warp);
@@ -823,7 +825,7 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
   uint32_t* kmeta = cmask + kChunk * kChunkWords;   // [max_det] class << 16 | next kept box of the same class bucket
   unsigned char* calive = reinterpret_cast<unsigned char*>(kmeta + P.max_det);
   __shared__ uint32_t s_alive[kChunkWords], s_new[kChunkWords];
-  __shared__ int s_K, s_cnt;
+  __shared__ int s_K, s_cnt, s_longrun;
   __shared__ uint32_t s_sel[2];
   // Class buckets: with the 4096-px class offset (general.py:702) two boxes of different classes cannot intersect as
   // long as the un-offset x extent of everything seen so far stays below kBucketExtent, so a candidate only needs the
@@ -889,7 +891,34 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       }
       __syncthreads();
       YB_TS(2);
-      src = block_radix_sort(band_a, band_b, band_n, scratch);
+      // The band is sorted on the score word only (2-3 digit passes instead of 5); keys with equal scores -- rare, a
+      // handful per band -- are then put into index order in place by the thread that owns the start of their run.
+      // Runs longer than 32 (synthetic all-equal inputs) fall back to a full 64-bit stable sort of the band.
+      {
+        uint64_t* sorted = block_radix_sort(band_a, band_b, band_n, scratch, 0xffffffff00000000ull);
+        if (tid == 0) s_longrun = 0;
+        __syncthreads();
+        for (int i = tid; i < band_n; i += (int)blockDim.x) {
+          const uint32_t h = (uint32_t)(sorted[i] >> 32);
+          if (i + 1 < band_n && (uint32_t)(sorted[i + 1] >> 32) == h && (i == 0 || (uint32_t)(sorted[i - 1] >> 32) != h)) {
+            int e = i + 2;
+            while (e < band_n && (uint32_t)(sorted[e] >> 32) == h) ++e;
+            if (e - i > 32) {
+              s_longrun = 1;
+            } else {
+              for (int a = i + 1; a < e; ++a) {          // insertion sort of the run on the full key (index order)
+                const uint64_t k = sorted[a];
+                int q = a - 1;
+                while (q >= i && sorted[q] > k) { sorted[q + 1] = sorted[q]; --q; }
+                sorted[q + 1] = k;
+              }
+            }
+          }
+        }
+        __syncthreads();
+        if (s_longrun) sorted = block_radix_sort(sorted, sorted == band_a ? band_b : band_a, band_n, scratch);
+        src = sorted;
+      }
       YB_TS(3);
       lo = T;
       have_lo = true;
