@@ -740,11 +740,23 @@ __device__ void select_band(const uint64_t* keys, int n, uint32_t lo, bool have_
     for (int i = tid; i < nbins; i += (int)blockDim.x) hist[i] = 0;
     if (tid == 0) s_found = 0;
     __syncthreads();
-    for (int i = tid; i < n; i += (int)blockDim.x) {
-      const uint32_t h = (uint32_t)(keys[i] >> 32);
-      if (have_lo && h <= lo) continue;
-      if (pbits && (h >> (32 - pbits)) != prefix) continue;
-      atomicAdd(&hist[(h >> shift) & (uint32_t)(nbins - 1)], 1);
+    // four keys per thread in flight (the keys come from L2: one dependent load per iteration would serialise)
+    for (int i0 = tid; i0 < n; i0 += 4 * (int)blockDim.x) {
+      uint32_t hv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * (int)blockDim.x;
+        hv[u] = i < n ? (uint32_t)(keys[i] >> 32) : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * (int)blockDim.x;
+        const uint32_t h = hv[u];
+        if (i >= n) continue;
+        if (have_lo && h <= lo) continue;
+        if (pbits && (h >> (32 - pbits)) != prefix) continue;
+        atomicAdd(&hist[(h >> shift) & (uint32_t)(nbins - 1)], 1);
+      }
     }
     __syncthreads();
     // block scan: thread t owns bins [per*t, per*t + per)
@@ -808,16 +820,13 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
   const int m_total = min(n, P.max_nms);  // general.py:698-699
 
   // =============================== greedy NMS ================================================
-  float* kx1 = reinterpret_cast<float*>(smem_raw);
+  float4* cbox = reinterpret_cast<float4*>(smem_raw);   // chunk: offset boxes (x1, y1, x2, y2), one 16-byte load per test
+  float* kx1 = reinterpret_cast<float*>(cbox + kChunk);
   float* ky1 = kx1 + P.max_det;
   float* kx2 = ky1 + P.max_det;
   float* ky2 = kx2 + P.max_det;
   float* kar = ky2 + P.max_det;
-  float* cx1 = kar + P.max_det;  // chunk (offset boxes)
-  float* cy1 = cx1 + kChunk;
-  float* cx2 = cy1 + kChunk;
-  float* cy2 = cx2 + kChunk;
-  float* car = cy2 + kChunk;
+  float* car = kar + P.max_det;
   float* craw = car + kChunk;    // [kChunk][4] un-offset xyxy
   float* cconf = craw + 4 * kChunk;
   float* ccls = cconf + kChunk;
@@ -874,20 +883,24 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       __syncthreads();
       if (tid == 0) s_cnt = 0;
       __syncthreads();
-      for (int i0 = 0; i0 < n; i0 += (int)blockDim.x) {
-        const int i = i0 + tid;
-        unsigned long long key = 0ull;
-        bool sel = false;
-        if (i < n) {
-          key = gkeys[i];
-          const uint32_t h = (uint32_t)(key >> 32);
-          sel = (!have_lo || h > lo) && h <= T;
+      for (int i0 = 0; i0 < n; i0 += 4 * (int)blockDim.x) {      // four keys per thread in flight
+        unsigned long long kv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * (int)blockDim.x + tid;
+          kv[u] = i < n ? gkeys[i] : 0ull;
         }
-        const unsigned mk = __ballot_sync(0xffffffffu, sel);
-        int pos = 0;
-        if (lane == 0 && mk) pos = atomicAdd(&s_cnt, __popc(mk));
-        pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mk & ((1u << lane) - 1u));
-        if (sel) band_a[pos] = key;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * (int)blockDim.x + tid;
+          const uint32_t h = (uint32_t)(kv[u] >> 32);
+          const bool sel = i < n && (!have_lo || h > lo) && h <= T;
+          const unsigned mk = __ballot_sync(0xffffffffu, sel);
+          int pos = 0;
+          if (lane == 0 && mk) pos = atomicAdd(&s_cnt, __popc(mk));
+          pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mk & ((1u << lane) - 1u));
+          if (sel) band_a[pos] = kv[u];
+        }
       }
       __syncthreads();
       YB_TS(2);
@@ -944,7 +957,7 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       const float x1 = __fsub_rn(x, hw), y1 = __fsub_rn(y, hh), x2 = __fadd_rn(x, hw), y2 = __fadd_rn(y, hh);
       const float c = P.agnostic ? 0.0f : __fmul_rn((float)cls, kMaxWH);
       const float ox1 = __fadd_rn(x1, c), oy1 = __fadd_rn(y1, c), ox2 = __fadd_rn(x2, c), oy2 = __fadd_rn(y2, c);
-      cx1[tid] = ox1; cy1[tid] = oy1; cx2[tid] = ox2; cy2[tid] = oy2;
+      cbox[tid] = make_float4(ox1, oy1, ox2, oy2);
       car[tid] = __fmul_rn(__fsub_rn(ox2, ox1), __fsub_rn(oy2, oy1));
       craw[4 * tid + 0] = x1; craw[4 * tid + 1] = y1; craw[4 * tid + 2] = x2; craw[4 * tid + 3] = y2;
       cconf[tid] = conf; ccls[tid] = (float)cls;
@@ -967,7 +980,8 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       const int j = tid >> pshift, part = tid & (parts - 1);
       bool sup = false;
       if (j < cnt) {
-        const float jx1 = cx1[j], jy1 = cy1[j], jx2 = cx2[j], jy2 = cy2[j], ja = car[j];
+        const float4 jb = cbox[j];
+        const float jx1 = jb.x, jy1 = jb.y, jx2 = jb.z, jy2 = jb.w, ja = car[j];
         const uint32_t cj = (uint32_t)ccls[j];
         // every thread of the candidate walks the whole chain (dependent loads), so the chain only pays when it is
         // much shorter than this thread's share of the kept array (one dominant class -> array scan)
@@ -1004,12 +1018,15 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
       const int warp = tid >> 5, nwarps = (int)blockDim.x >> 5;
       for (int i = warp; i < cnt; i += nwarps) {
         if (!calive[i]) continue;
-        const float ix1 = cx1[i], iy1 = cy1[i], ix2 = cx2[i], iy2 = cy2[i], ia = car[i], ci = ccls[i];
+        const float4 ib = cbox[i];
+        const float ix1 = ib.x, iy1 = ib.y, ix2 = ib.z, iy2 = ib.w, ia = car[i], ci = ccls[i];
         for (int w = i >> 5; w < kChunkWords; ++w) {
           const int j = w * 32 + lane;
           bool sup = false;
-          if (j > i && j < cnt && calive[j] && (!bucket_mode || ccls[j] == ci))
-            sup = iou_suppresses(ix1, iy1, ix2, iy2, ia, cx1[j], cy1[j], cx2[j], cy2[j], car[j], P.thr_f, P.thr_nonneg);
+          if (j > i && j < cnt && calive[j] && (!bucket_mode || ccls[j] == ci)) {
+            const float4 jb = cbox[j];
+            sup = iou_suppresses(ix1, iy1, ix2, iy2, ia, jb.x, jb.y, jb.z, jb.w, car[j], P.thr_f, P.thr_nonneg);
+          }
           const uint32_t word = __ballot_sync(0xffffffffu, sup);
           if (lane == 0) cmask[i * kChunkWords + w] = word;
         }
@@ -1068,7 +1085,8 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
     if (tid < cnt && ((s_new[tid >> 5] >> (tid & 31)) & 1u)) {
       int pos = K + __popc(s_new[tid >> 5] & ((1u << (tid & 31)) - 1u));
       for (int w = 0; w < (tid >> 5); ++w) pos += __popc(s_new[w]);
-      kx1[pos] = cx1[tid]; ky1[pos] = cy1[tid]; kx2[pos] = cx2[tid]; ky2[pos] = cy2[tid]; kar[pos] = car[tid];
+      const float4 nb = cbox[tid];
+      kx1[pos] = nb.x; ky1[pos] = nb.y; kx2[pos] = nb.z; ky2[pos] = nb.w; kar[pos] = car[tid];
       if (bucket_mode) {
         const uint32_t cj = (uint32_t)ccls[tid];
         kmeta[pos] = (cj << 16) | (uint32_t)atomicExch(&s_khead[cj & (kBuckets - 1)], pos);
