@@ -1,7 +1,7 @@
 #!/bin/bash
 mkdir -p gpurun_out
-python bench.py --model yolov7-tiny --batch 1 --steps 3 --warmup 3 --no-extras > gpurun_out/b1_plain.json 2>/dev/null || exit 1
-ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/b1_launches.csv python bench.py --model yolov7-tiny --batch 1 --steps 3 --warmup 3 --no-extras > /dev/null 2>&1
+python bench.py --model ${MODEL:-yolov7-tiny} --batch 1 --steps 3 --warmup 3 --no-extras > gpurun_out/b1_plain.json 2>/dev/null || exit 1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/b1_launches.csv python bench.py --model ${MODEL:-yolov7-tiny} --batch 1 --steps 3 --warmup 3 --no-extras > /dev/null 2>&1
 python - <<'PY'
 import csv
 rows=[r for r in csv.reader(l for l in open('gpurun_out/b1_launches.csv') if not l.startswith('=='))]
