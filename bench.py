@@ -25,6 +25,26 @@ if ROOT not in sys.path:
 
 MODEL, IMG, BATCH = 'yolov7', 640, 32
 CONF, IOU, MAX_DET = 0.001, 0.65, 300
+
+
+def metric_name(model, img):
+    """ONE string for both arms (the driver divides the two lines only when metric / unit / direction agree); the
+    arithmetic type lives in `dtype`, not in the name."""
+    return f'{model} {img} e2e images/sec (forward+decode+NMS)'
+
+
+def workload_name(model, img, batch):
+    return f'{model} {img}x{img} batch {batch}/GPU, RepConv/BN folded, conf {CONF} iou {IOU} max_det {MAX_DET}'
+
+
+def cpu_model():
+    try:
+        for l in open('/proc/cpuinfo'):
+            if l.startswith('model name'):
+                return l.split(':', 1)[1].strip()
+    except OSError:
+        pass
+    return 'unknown'
 FALLBACK_PEAKS = {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0}
 
 
@@ -108,29 +128,33 @@ def cpu_reference_step(cfg, sd, imgs, threads):
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference algorithm on the host cores (rank 0 only)."""
+    """--impl reference: the reference algorithm on the host cores (rank 0 only), same metric / config strings as the
+    repo arm; each step is a bounded sample (8 images) of the configured batch."""
     if rank != 0:
         return
     import torch
     from yolo_series_b200 import Model, zoo
     from yolo_series_b200.synth import seeded_state_dict, synth_image
     threads = os.cpu_count() or 1
-    sample = 8  # images per step: bounded so that K steps finish within minutes (~1 s/step on 16 cores)
-    cfg = zoo.get_cfg(MODEL)
+    model_name, img = args.model, args.img
+    # images per step: bounded so that K steps finish within minutes (yolov7 640: ~1 s/step on 16 cores)
+    sample = 8 if img <= 640 else 2
+    cfg = zoo.get_cfg(model_name)
     sd = seeded_state_dict(Model(cfg), seed=0)
-    imgs = synth_image(sample, IMG, IMG, seed=2)
+    imgs = synth_image(sample, img, img, seed=2)
     for _ in range(args.warmup):
         cpu_reference_step(cfg, sd, imgs, threads)
     t = sum(cpu_reference_step(cfg, sd, imgs, threads) for _ in range(args.steps))
     v = sample * args.steps / t
     line = {
-        'impl': 'reference', 'metric': 'yolov7 640 e2e images/sec (forward+decode+NMS)', 'value': v,
+        'impl': 'reference', 'metric': metric_name(model_name, img), 'value': v,
         'unit': 'images/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': 1e3 * t / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'f32', 'data': 'synthetic',
-        'config': {'workload': f'{MODEL} {IMG}x{IMG} conf {CONF} iou {IOU} max_det {MAX_DET}, {sample} images/step on host CPU',
-                   'batch_per_step': sample},
-        'cpu_baseline': {'value': v, 'unit': 'images/s', 'cores': threads, 'kind': 'port',
+        'config': {'workload': workload_name(model_name, img, args.batch), 'batch_per_gpu': args.batch,
+                   'sample': f'{sample} images/step of that workload on the host CPU ({threads} threads, {cpu_model()})',
+                   'images_per_step': sample},
+        'cpu_baseline': {'value': v, 'unit': 'images/s', 'cores': threads, 'kind': 'port', 'cpu': cpu_model(),
                          'sample': f'{sample} images/step x {args.steps} steps, fp32 torch CPU kernels + oracle NMS'},
         'e2e': {'value': v, 'unit': 'images/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
@@ -138,8 +162,9 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def nms_stress(dev, peaks):
-    """BASELINE.json configs[4]: 100k candidates/image, 80 classes, max_det 1000, batch 256 (8.7 GB)."""
+def nms_stress(dev, peaks, cpu_images=8):
+    """BASELINE.json configs[4]: 100k candidates/image, 80 classes, max_det 1000, batch 256 (8.7 GB) -- the GPU path in
+    us/image next to the reference algorithm on the host cores (second half of BASELINE.json's metric)."""
     import torch
     from yolo_series_b200.nms import _run_nms
     B, A, nc = 256, 100000, 80
@@ -173,9 +198,109 @@ def nms_stress(dev, peaks):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / reps
     algo_bytes = B * A * (nc + 5) * 4 + B * 1000 * 6 * 4 + B * 4
-    return {'us_per_image': 1e3 * ms / B, 'batch': B, 'rows_per_image': A, 'max_det': 1000,
-            'kept_mean': float(meta[:B].float().mean()), 'algorithmic_GBps': algo_bytes / ms / 1e6,
-            'frac_of_hbm_peak': algo_bytes / ms / 1e6 / peaks['hbm_gbs']}
+    res = {'us_per_image': 1e3 * ms / B, 'batch': B, 'rows_per_image': A, 'max_det': 1000,
+           'kept_mean': float(meta[:B].float().mean()), 'algorithmic_GBps': algo_bytes / ms / 1e6,
+           'frac_of_hbm_peak': algo_bytes / ms / 1e6 / peaks['hbm_gbs']}
+    # ---- CPU leg of "NMS us/image vs CPU ref" (SURVEY.md 8d): the reference algorithm (oracle restatement of
+    # general.py:628-720 with max_det as a parameter, one image per call so no time_limit applies) on a fixed subset of
+    # the SAME batch, with all host threads and with one; the GPU rows of those images are checked against it.
+    import numpy as np
+    from oracle.nms_ref import non_max_suppression_ref
+    sub = list(range(0, B, B // cpu_images))[:cpu_images]
+    host = pred[sub].cpu()
+    counts = meta[:B].cpu()
+    gpu_rows = [out[i, :int(counts[i])].cpu().numpy() for i in sub]
+    del pred
+    threads = os.cpu_count() or 1
+
+    def cpu_leg(nthreads, idx):
+        torch.set_num_threads(nthreads)
+        t0, outs = time.perf_counter(), []
+        for j in idx:
+            outs.append(non_max_suppression_ref(host[j:j + 1], 0.001, 0.65, max_det=1000, max_nms=30000)[0].numpy())
+        return (time.perf_counter() - t0) / len(idx), outs
+    t_all, ref_rows = cpu_leg(threads, range(len(sub)))
+    t_one, _ = cpu_leg(1, range(min(2, len(sub))))
+    torch.set_num_threads(threads)
+    res.update({'cpu_us_per_image': 1e6 * t_all, 'cpu_threads': threads, 'cpu_us_per_image_1thread': 1e6 * t_one,
+                'cpu_model': cpu_model(), 'cpu_kind': 'port (oracle/nms_ref.py + oracle/nms_greedy.c)',
+                'cpu_sample': f'images {sub} of the {B}-image batch ({len(sub)} images, all threads; first '
+                              f'{min(2, len(sub))} with 1 thread)',
+                'gpu_vs_cpu': t_all * 1e6 / (1e3 * ms / B),
+                'parity_on_sample': 'bit-identical' if all(np.array_equal(a, b) for a, b in zip(gpu_rows, ref_rows))
+                                    else 'MISMATCH'})
+    return res
+
+
+def trunk_and_nms_ms(model, eng, reps=10):
+    """Device time of the captured trunk graph alone and of the fused decode+NMS alone (CUDA events on the
+    launching stream, after warm-up).  Both run back to back inside every timed step, so each is <= ms_per_step."""
+    import torch
+    from yolo_series_b200.nms import _run_nms
+    lv, head = model.head_levels(eng)
+    A = sum(head.na * v.H * v.W for v in eng.head_views)
+    nms = lambda: _run_nms(None, eng.B, A, head.no, CONF, IOU, None, False, False, 30000, MAX_DET, eng.device,
+                           levels=(lv, head.nl, head.na), return_packed=True)
+    e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    for _ in range(2):
+        eng.run(); nms()
+    torch.cuda.synchronize()
+    t_trunk = t_nms = 0.0
+    for _ in range(reps):
+        e[0].record(); eng.run(); e[1].record(); nms(); e[2].record()
+        torch.cuda.synchronize()
+        t_trunk += e[0].elapsed_time(e[1]); t_nms += e[1].elapsed_time(e[2])
+    return t_trunk / reps, t_nms / reps, A, head.no
+
+
+def kernel_rooflines(model, eng, peaks, peak_src, traffic_by_kernel):
+    """One roofline entry per kernel of the step.  Per-op times come from an eager pass with a CUDA event between
+    consecutive ops (yb_engine_profile); that pass runs without the graph's programmatic-dependent-launch overlap, so
+    its per-kernel SHARES are applied to the measured time of the captured trunk graph -- every `ms` below is a slice
+    of the timed step.  Bound of a kernel = the slower of FLOPs / sustained bf16 peak and algorithmic bytes / HBM copy
+    peak, summed over its launches (per-layer bound); frac = bound time / measured time."""
+    trunk_ms, nms_ms, A, no = trunk_and_nms_ms(model, eng)
+    table = eng.profile_table(3)
+    eager_ms = sum(r['ms'] for r in table)
+    tf_peak, hbm_peak = peaks['bf16_tflops_sustained'], peaks['hbm_gbs']
+    groups = {}
+    for r in table:
+        g = groups.setdefault(r['kernel'], {'launches': 0, 'ms_eager': 0.0, 'flops': 0, 'bytes': 0, 'bound_ms': 0.0,
+                                            't_tensor': 0.0, 't_hbm': 0.0})
+        tt, th = r['flops'] / (tf_peak * 1e9), r['bytes'] / (hbm_peak * 1e6)
+        g['launches'] += 1; g['ms_eager'] += r['ms']; g['flops'] += r['flops']; g['bytes'] += r['bytes']
+        g['bound_ms'] += max(tt, th); g['t_tensor'] += tt; g['t_hbm'] += th
+    out = []
+    for k, g in groups.items():
+        ms = g['ms_eager'] * trunk_ms / eager_ms
+        tensor = g['t_tensor'] >= g['t_hbm']
+        ach = g['flops'] / ms / 1e9 if tensor else g['bytes'] / ms / 1e6
+        out.append({'kernel': k, 'launches': g['launches'], 'ms': ms, 'bound': 'tensor' if tensor else 'hbm',
+                    'achieved': ach, 'peak': tf_peak if tensor else hbm_peak, 'unit': 'TFLOP/s' if tensor else 'GB/s',
+                    'frac': ach / (tf_peak if tensor else hbm_peak), 'frac_of_layer_bound': g['bound_ms'] / ms,
+                    'tflops': g['flops'] / ms / 1e9, 'algorithmic_GBps': g['bytes'] / ms / 1e6,
+                    'flops': g['flops'], 'bytes': g['bytes'], 'traffic': traffic_by_kernel.get(k)})
+    nms_bytes = eng.B * A * no * 4 + eng.B * MAX_DET * 24 + eng.B * 4
+    out.append({'kernel': 'k_filter_cells+k_sort_nms', 'launches': 2, 'ms': nms_ms, 'bound': 'hbm',
+                'achieved': nms_bytes / nms_ms / 1e6, 'peak': hbm_peak, 'unit': 'GB/s',
+                'frac': nms_bytes / nms_ms / 1e6 / hbm_peak, 'frac_of_layer_bound': nms_bytes / nms_ms / 1e6 / hbm_peak,
+                'flops': 0, 'bytes': nms_bytes,
+                'traffic': (traffic_by_kernel.get('k_filter_cells', 0) + traffic_by_kernel.get('k_sort_nms', 0)) or None})
+    out.sort(key=lambda r: -r['ms'])
+    for r in out:
+        for k in ('ms', 'achieved', 'frac', 'frac_of_layer_bound', 'tflops', 'algorithmic_GBps'):
+            if k in r:
+                r[k] = round(r[k], 4)
+    conv = [r for r in out if r['kernel'].startswith(('k_conv', 'k_stem'))]
+    summary = {'trunk_graph_ms': round(trunk_ms, 4), 'decode_nms_ms': round(nms_ms, 4),
+               'eager_per_op_sum_ms': round(eager_ms, 4),
+               'conv_ms': round(sum(r['ms'] for r in conv), 4),
+               'conv_tflops': round(sum(r['flops'] for r in conv) / sum(r['ms'] for r in conv) / 1e9, 1),
+               'conv_frac_of_sustained_bf16': round(sum(r['flops'] for r in conv) / sum(r['ms'] for r in conv) / 1e9 / tf_peak, 4),
+               'step_frac_of_layer_bounds': round(sum(r['frac_of_layer_bound'] * r['ms'] for r in out) / sum(r['ms'] for r in out), 4),
+               'method': 'per-kernel shares of an eager per-op event pass applied to the CUDA-event time of the captured trunk graph',
+               'peaks': f'{peak_src}: bf16 sustained {tf_peak} TFLOP/s, HBM copy {hbm_peak} GB/s'}
+    return out, summary, table
 
 
 def main():
@@ -301,6 +426,30 @@ def main():
         t = torch.tensor([ms_dev, ms_e2e, ms_e2e_serial], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_dev, ms_e2e, ms_e2e_serial = float(t[0]), float(t[1]), float(t[2])
+    # ---- N > 1: correctness of the exchange, outside the timed region.  Rank 0 regenerates every rank's seeded shard,
+    # runs it through its own replica (no gather) and compares with the block that arrived for that rank.
+    gather_check = None
+    if world > 1:
+        if pg is not None:
+            out_all, meta_all = step_device()
+            cnt_all = meta_all[:B * world]
+        else:
+            o, m = model.detect(x_dev, CONF, IOU, max_det=MAX_DET, packed=True)
+            out_all, cnt_all = ydist.gather_detections(o, m[:B])
+        torch.cuda.synchronize()
+        if rank == 0:
+            ok = True
+            for r in range(world):
+                xr = synth_image(B, img, img, seed=100 + r, dtype=torch.uint8).to(dev)
+                o_r, m_r = model.detect(xr, CONF, IOU, max_det=MAX_DET, packed=True)
+                c_r = m_r[:B]
+                blk_o, blk_c = out_all[r * B:(r + 1) * B], cnt_all[r * B:(r + 1) * B]
+                ok &= bool(torch.equal(blk_c.to(torch.int32), c_r.to(torch.int32)))
+                for i in range(B):
+                    n = int(c_r[i])
+                    ok &= bool(torch.equal(blk_o[i, :n], o_r[i, :n]))
+            gather_check = 'bit-identical' if ok else 'MISMATCH'
+        barrier()
     if pg is not None:
         pg.check()
         pg.close()
@@ -312,15 +461,17 @@ def main():
     n_imgs = B * world * args.steps
     launches_per_step = 1 + eng.num_launches() + 2     # stage + trunk ops + k_filter + k_sort_nms
     line = {
-        'metric': f'{model_name} {img} bf16 e2e images/sec (forward+decode+NMS)', 'value': n_imgs / (ms_dev / 1e3),
+        'metric': metric_name(model_name, img), 'value': n_imgs / (ms_dev / 1e3),
         'unit': 'images/s', 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
         'ms_per_step': ms_dev / args.steps, 'higher_is_better': True, 'scaling': scaling, 'vs_baseline': None,
         'dtype': 'bf16', 'data': 'synthetic',
-        'config': {'workload': f'{model_name} {img}x{img} batch {B}/GPU bf16, RepConv/BN folded, conf {CONF} iou {IOU} max_det {MAX_DET}',
+        'value_note': 'inputs resident in HBM (uint8 batch on the device); the host-to-host figure is e2e.value',
+        'config': {'workload': workload_name(model_name, img, B),
                    'batch_per_gpu': B, 'global_batch': B * world, 'parallelism': f'image-sharded replicas x{world}',
                    'gather': ('none' if world == 1 else 'in-kernel P2P stores over NVLink (yb_decode_nms_gather)' if use_peer
                               else 'NCCL all_gather'),
-                   'l2': 'no flush: per-step working set (activations, GBs) >> 126 MB L2'},
+                   'l2': 'no flush: per-step working set (activations, GBs) >> 126 MB L2',
+                   'input': 'one seeded pinned uint8 batch per rank, re-sent H2D every e2e step'},
         'e2e': {'value': n_imgs / (ms_e2e / 1e3), 'unit': 'images/s', 'h2d_bytes_per_step': x_host.numel(),
                 'd2h_bytes_per_step': int(res.numel() * 4 + cnt.numel() * 4 + 4), 'ms_per_step': ms_e2e / args.steps,
                 'api': 'Model.detect_batches (H2D / compute / D2H on three streams, two slots)',
@@ -330,33 +481,34 @@ def main():
         'clocks': clocks,
         'detections_per_image': float(cnt.float().mean()),
     }
+    if gather_check is not None:
+        line['gather_check'] = gather_check
     if not args.no_extras:
-        # ---- roofline of the dominant kernel (k_conv_tc): CUDA events around every op of an eager pass
-        prof = [eng.profile() for _ in range(3)][-1]
-        conv_ms = sum(r[2] for r in prof if r[1] == 1)
-        all_ms = sum(r[2] for r in prof)
-        flops = sum(r[3] for r in prof)
-        ach = flops / (conv_ms / 1e3) / 1e12
-        n_conv = sum(1 for r in prof if r[1] == 1)
-        traffic, traffic_src = None, None
-        try:   # (headline workload only) DRAM bytes of the conv launches of one step, from the committed ncu launch list (cold-cache per launch)
+        # ---- per-kernel rooflines; `roofline` = the kernel with the largest share of the step
+        traffic, traffic_src = {}, None
+        try:   # DRAM bytes per kernel of one step from the committed ncu launch list (cold-cache per launch)
             if not headline:
                 raise KeyError('launch list exists for the headline workload only')
-            summ = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'profiles',
-                                               'round1_launch_summary.json')))
-            traffic = summ['conv_dram_bytes_per_step']
-            traffic_src = 'profiles/round1_launch_summary.json (ncu dram__bytes_read+write, sum over the conv launches of one step)'
+            tp = os.path.join(ROOT, 'profiles', 'round2_launch_summary.json')
+            if not os.path.exists(tp):
+                tp = os.path.join(ROOT, 'profiles', 'round1_launch_summary.json')
+            for k in json.load(open(tp))['kernels']:
+                traffic[k['kernel'].split('<')[0]] = k['dram_bytes']
+            traffic_src = os.path.relpath(tp, ROOT) + ' (ncu dram__bytes_read+write summed over the kernel\'s launches of one step)'
         except Exception:  # noqa: BLE001
             pass
-        line['roofline'] = {'bound': 'tensor', 'kernel': f'tcgen05 conv kernels k_conv_tc / k_conv3_tc / k_conv3s2p_tc / k_stem_tc ({n_conv} launches/step)',
-                            'achieved': ach,
-                            'peak': peaks['bf16_tflops_sustained'], 'peak_source': peak_src + ' (sustained bf16 cuBLAS)',
-                            'unit': 'TFLOP/s', 'frac': ach / peaks['bf16_tflops_sustained'], 'traffic': traffic,
-                            'traffic_source': traffic_src,
-                            'flops_per_step': flops, 'conv_ms_per_step': conv_ms, 'trunk_ms_per_step_eager': all_ms,
-                            'conv_share_of_trunk': conv_ms / all_ms}
-        top = sorted(prof, key=lambda r: -r[2])[:8]
-        line['top_ops'] = [{'op': r[0], 'ms': round(r[2], 4), 'tflops': round(r[3] / r[2] / 1e9, 1) if r[3] else None} for r in top]
+        kernels, summary, table = kernel_rooflines(model, eng, peaks, peak_src, traffic)
+        top = dict(kernels[0])
+        line['roofline'] = {'bound': top['bound'], 'achieved': top['achieved'], 'peak': top['peak'], 'unit': top['unit'],
+                            'frac': top['frac'], 'traffic': top['traffic'], 'kernel': top['kernel'],
+                            'launches_per_step': top['launches'], 'ms_per_step': top['ms'],
+                            'frac_of_layer_bound': top['frac_of_layer_bound'],
+                            'peak_source': peak_src + (' (sustained bf16 cuBLAS)' if top['bound'] == 'tensor' else ' (HBM copy)'),
+                            'traffic_source': traffic_src, **summary}
+        line['roofline_kernels'] = kernels
+        line['top_ops'] = [{'op': r['op'], 'kernel': r['kernel'], 'ms_eager': round(r['ms'], 4),
+                            'tflops': round(r['flops'] / r['ms'] / 1e9, 1) if r['flops'] else None,
+                            'GBps': round(r['bytes'] / r['ms'] / 1e6)} for r in sorted(table, key=lambda r: -r['ms'])[:8]]
         if world == 1 and headline:
             try:
                 line['nms_stress'] = nms_stress(dev, peaks)
@@ -372,6 +524,7 @@ def main():
             reps = 10      # ~10-15 s of host work
             t = sum(cpu_reference_step(cfg, sd, imgs, threads) for _ in range(reps))
             line['cpu_baseline'] = {'value': nimg * reps / t, 'unit': 'images/s', 'cores': threads, 'kind': 'port',
+                                    'cpu': cpu_model(),
                                     'sample': f'{nimg * reps} images ({reps} steps of {nimg}) of the same workload, fp32 torch CPU + oracle NMS'}
     print(json.dumps(line), flush=True)
     if world > 1:

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define YB_ABI_VERSION 1
+#define YB_ABI_VERSION 2
 
 typedef enum {
   YB_OK = 0,
@@ -164,6 +164,9 @@ int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no, float con
  * buffer of every GPU of the box over NVLink (peer-to-peer stores into CUDA-IPC mapped memory), and the last CTA
  * raises the sender's arrival flag on every peer (fence.sys + st.release.sys).  yb_peer_wait is the receive side:
  * one warp polls this rank's flags until every sender has reached `step`.  No NCCL call, no packing kernels.
+ * A sender that does not arrive within `timeout_ms` (0 = 20 s) is reported, never silently ignored: bit 8 of *status
+ * is set and the B entries of that sender's block of `counts` (this rank's receive buffer, nullable) are overwritten
+ * with -1, so a stale block can not be mistaken for detections.
  *   out[p]    peer p's receive buffer, (n_peers, B, max_det, 6) fp32: this rank writes block `rank`
  *   counts[p] peer p's (n_peers, B) int32;  flags[p]: peer p's (n_peers) uint32 arrival counters
  *   step      strictly increasing per use of a buffer set (> 0); done_counter: local device int, zero-initialised
@@ -185,7 +188,8 @@ int yb_decode_nms_gather(const yb_head_level* levels, int nl, int na, int no, fl
                          int max_nms, int max_det, int cand_cap, void* workspace, size_t workspace_bytes,
                          float* out, int* counts, int* overflow, const yb_peer_gather* peer /* nullable */,
                          void* stream);
-int yb_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, int* status /* device, nullable */, void* stream);
+int yb_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, int* status /* device, nullable */,
+                 int32_t* counts /* device (n_peers, B), nullable */, int B, unsigned timeout_ms, void* stream);
 int yb_peer_alloc(size_t bytes, void** ptr, unsigned char handle[64]);
 int yb_peer_open(const unsigned char handle[64], void** ptr);
 int yb_peer_close(void* ptr);
@@ -222,6 +226,9 @@ int yb_engine_forward(yb_engine* e, int use_graph, void* stream);
 /* eager run with a CUDA event between consecutive ops; ms_per_op[n_ops] (synchronises `stream`) */
 int yb_engine_profile(yb_engine* e, float* ms_per_op, void* stream);
 int yb_engine_num_launches(const yb_engine* e);
+/* name of the CUDA kernel op `i` launches ("k_conv_tc", "k_conv3_tc", "k_maxpool2", ...); NULL if out of range.
+ * Used by bench.py to group the per-op times of yb_engine_profile into per-kernel roofline entries. */
+const char* yb_engine_op_kernel(const yb_engine* e, int i);
 void yb_engine_destroy(yb_engine* e);
 
 /* ------------------------------------------------------------------ pre-processing

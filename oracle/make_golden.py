@@ -28,6 +28,13 @@ FWD_CASES = [
 ]
 # BASELINE.json configs[0]: yolov7-tiny 1x3x640x640, detect.py defaults
 E2E_CASE = ('yolov7-tiny', 1, 640, 640, 0.25, 0.45)
+# BASELINE.json configs[1]-[3] at their REAL resolutions (round 2): the reference's own models.yolo.Model forward
+# (yolo.py:581-631) + non_max_suppression; stored as detections + every 37th row of pred (the npz stays small)
+FULL_CASES = [
+    ('yolov7', 2, 640, 640, 0.001, 0.65),
+    ('yolov7-w6-custom', 1, 1280, 1280, 0.001, 0.65),
+    ('yolov7-e6e', 1, 1280, 1280, 0.001, 0.65),
+]
 
 # NMS fixtures: (tag, B, A, nc, seed, p_obj, kwargs)
 NMS_CASES = [
@@ -38,6 +45,13 @@ NMS_CASES = [
     ('nc1', 2, 2000, 1, 15, 0.5, dict(conf_thres=0.25, iou_thres=0.45)),
     ('empty', 2, 500, 80, 16, 0.0, dict(conf_thres=0.25, iou_thres=0.45)),
     ('cut', 1, 40000, 4, 17, 1.0, dict(conf_thres=0.001, iou_thres=0.65)),   # > max_nms candidates
+]
+
+# Cross-class suppression (general.py:702-704: the 4096-px class offset does not separate boxes larger than 4096 px):
+# (tag, B, A, nc, seed, mixed, kwargs) over oracle.synth.synth_pred_wide
+WIDE_CASES = [
+    ('wide', 2, 3000, 80, 31, False, dict(conf_thres=0.1, iou_thres=0.05)),
+    ('wide_mixed', 2, 3000, 80, 32, True, dict(conf_thres=0.1, iou_thres=0.05)),
 ]
 
 
@@ -65,12 +79,13 @@ def dets_to_np(dets):
 
 def main():
     sys.path.insert(0, ROOT)
-    from oracle.synth import seeded_state_dict, synth_image, synth_pred
+    from oracle.synth import seeded_state_dict, synth_image, synth_pred, synth_pred_wide
     from yolo_series_b200 import zoo
     RefModel, ref_nms = import_reference()
     os.makedirs(GOLD, exist_ok=True)
     with torch.no_grad():
-        for name, B, H, W, conf, iou in FWD_CASES + [E2E_CASE]:
+        only_full = '--full-only' in sys.argv
+        for name, B, H, W, conf, iou in ([] if only_full else FWD_CASES + [E2E_CASE]) + ([] if '--wide' in sys.argv else FULL_CASES):
             cfg = zoo.get_cfg(name)
             ref = RefModel(cfg).eval()
             sd = seeded_state_dict(ref, seed=0)
@@ -81,7 +96,7 @@ def main():
             dets = [ref_nms(pred[i:i + 1], conf, iou)[0] for i in range(B)]   # per image: no time_limit drop
             counts, flat = dets_to_np(dets)
             tag = f'{name}_{H}x{W}'
-            full = (H, W) != (640, 640)
+            full = max(H, W) < 640
             out = dict(counts=counts, dets=flat, conf=conf, iou=iou, shape=np.array(pred.shape),
                        cand=np.array([(pred[..., 4] > conf).sum().item()]))
             if full:
@@ -91,8 +106,14 @@ def main():
                 out['pred_sub'] = pred[:, ::37].numpy()
             np.savez_compressed(os.path.join(GOLD, f'fwd_{tag}.npz'), **out)
             print(tag, 'pred', tuple(pred.shape), 'candidates', int(out['cand'][0]), 'dets', counts.tolist())
-        for tag, B, A, nc, seed, p_obj, kw in NMS_CASES:
+        for tag, B, A, nc, seed, p_obj, kw in ([] if only_full else NMS_CASES):
             pred = synth_pred(B, A, nc, seed=seed, p_obj=p_obj)
+            dets = [ref_nms(pred[i:i + 1].clone(), **kw)[0] for i in range(B)]
+            counts, flat = dets_to_np(dets)
+            np.savez_compressed(os.path.join(GOLD, f'nms_{tag}.npz'), counts=counts, dets=flat)
+            print('nms', tag, counts.tolist())
+        for tag, B, A, nc, seed, mixed, kw in ([] if (only_full and '--wide' not in sys.argv) else WIDE_CASES):
+            pred = synth_pred_wide(B, A, nc, seed=seed, mixed=mixed)
             dets = [ref_nms(pred[i:i + 1].clone(), **kw)[0] for i in range(B)]
             counts, flat = dets_to_np(dets)
             np.savez_compressed(os.path.join(GOLD, f'nms_{tag}.npz'), counts=counts, dets=flat)

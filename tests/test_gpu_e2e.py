@@ -172,6 +172,17 @@ def test_peer_gather_single_rank_equals_detect():
             pg.begin(8, 50)
         pg.close()
         assert int(want_meta[:4].sum()) > 0
+        # a sender that never arrives: the bounded wait must poison its block (counts = -1) and set the status word, and
+        # the host-side read-back paths must raise instead of returning stale rows
+        late = ydist.PeerGather(4, 50, timeout_s=0.05)
+        _, slot, step = late.begin(4, 50)          # no NMS launch follows: the flag for `step` is never raised
+        _, cnt = late.finish(slot, step)
+        assert cnt.tolist() == [-1, -1, -1, -1]
+        with pytest.raises(RuntimeError, match='timed out'):
+            late.check()
+        with pytest.raises(RuntimeError, match='timed out'):
+            late.raise_if_poisoned(cnt.cpu())
+        late.close()
     finally:
         dist.destroy_process_group()
 
@@ -190,3 +201,36 @@ def test_accelerate_wrapper_runs_the_engine():
     d0, d1 = non_max_suppression(p0, 0.05, 0.5), acc.detect(x, 0.05, 0.5)
     assert all(torch.equal(a, b) for a, b in zip(d0, d1))
     assert acc.stride.tolist() == [8., 16., 32.] and next(acc.parameters()).is_cuda
+
+
+def test_engine_cache_is_a_bounded_lru_sharing_packed_weights():
+    """Model._engines: shape-specialised engines are evicted least-recently-used and destroyed; the packed
+    weights are shared between engines of one model; results do not depend on cache state."""
+    m = _build('yolov7-tiny', 'bf16')
+    m.engine_cache_size = 2
+    xs = [synth_image(1, 64 + 32 * i, 96, seed=30 + i, dtype=torch.uint8).cuda() for i in range(3)]
+    first = m.detect(xs[0], 0.05, 0.5, max_det=50, packed=True)
+    first = (first[0].clone(), first[1].clone())
+    n_packed = len(m._packed)
+    e0 = next(iter(m._engines.values()))
+    m.detect(xs[1], 0.05, 0.5, max_det=50)
+    m.detect(xs[2], 0.05, 0.5, max_det=50)
+    assert len(m._engines) == 2 and len(m._packed) == n_packed
+    assert e0.handle is None, 'the evicted engine must have been destroyed'
+    engines = list(m._engines.values())
+    assert engines[0].weights[0].data_ptr() == engines[1].weights[0].data_ptr()
+    again = m.detect(xs[0], 0.05, 0.5, max_det=50, packed=True)      # rebuilt after eviction: same bits
+    assert torch.equal(again[1], first[1])
+    n = int(first[1][0])
+    assert torch.equal(again[0][0, :n], first[0][0, :n])
+
+
+def test_forward_profile_prints_per_op_table(capsys):
+    """model(x, profile=True) (yolo.py:614-623): per-op device times are printed, results are unchanged."""
+    m = _build('yolov7-tiny', 'bf16')
+    x = synth_image(1, 64, 96, seed=3, dtype=torch.uint8).cuda()
+    a = m(x)[0]
+    b = m(x, profile=True)[0]
+    assert torch.equal(a, b)
+    txt = capsys.readouterr().out
+    assert 'k_conv' in txt and 'ms total' in txt

@@ -4,9 +4,9 @@ import numpy as np
 import pytest
 import torch
 
-from oracle.make_golden import NMS_CASES
+from oracle.make_golden import NMS_CASES, WIDE_CASES
 from oracle.nms_ref import non_max_suppression_ref
-from oracle.synth import synth_pred
+from oracle.synth import synth_pred, synth_pred_wide
 
 pytestmark = pytest.mark.gpu
 
@@ -24,6 +24,28 @@ def test_nms_equals_reference_golden(case, gold):
     out = non_max_suppression(pred, **kw)
     assert [o.shape[0] for o in out] == g['counts'].tolist()
     assert np.array_equal(_flat(out), g['dets'])
+
+
+@pytest.mark.parametrize('case', WIDE_CASES, ids=[c[0] for c in WIDE_CASES])
+def test_nms_cross_class_suppression(case, gold):
+    """Boxes of 6 000-9 000 px: after the 4096-px class offset (general.py:702-704) neighbouring classes overlap and
+    suppress each other.  k_sort_nms chains the kept set per class bucket only while the un-offset x extent of
+    everything seen stays < 4000 px and must drop that mode here -- at once ('wide') or after several chunks of narrow
+    boxes ('wide_mixed').  Bit-exact against the real reference's golden and the oracle; tests/test_oracle_nms.py proves
+    from the oracle side that suppressions do cross classes in these inputs."""
+    from yolo_series_b200 import non_max_suppression
+    tag, B, A, nc, seed, mixed, kw = case
+    g = gold(f'nms_{tag}.npz')
+    pred = synth_pred_wide(B, A, nc, seed=seed, mixed=mixed)
+    out = non_max_suppression(pred.cuda(), **kw)
+    assert [o.shape[0] for o in out] == g['counts'].tolist()
+    assert np.array_equal(_flat(out), g['dets'])
+    for extra in (dict(max_det=1000), dict(max_det=20), dict(agnostic=True), dict(multi_label=True)):
+        k2 = {**kw, **extra}
+        ref = non_max_suppression_ref(pred, **k2)
+        got = non_max_suppression(pred.cuda(), **k2)
+        assert [o.shape[0] for o in got] == [r.shape[0] for r in ref], extra
+        assert np.array_equal(_flat(got), _flat(ref)), extra
 
 
 @pytest.mark.parametrize('kw', [

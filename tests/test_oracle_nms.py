@@ -5,9 +5,9 @@ import numpy as np
 import pytest
 import torch
 
-from oracle.make_golden import NMS_CASES
+from oracle.make_golden import NMS_CASES, WIDE_CASES
 from oracle.nms_ref import greedy_nms, non_max_suppression_ref
-from oracle.synth import synth_pred
+from oracle.synth import synth_pred, synth_pred_wide
 
 tv = pytest.importorskip('torchvision')
 
@@ -53,6 +53,35 @@ def test_nms_ref_equals_reference_golden(case, gold):
     assert [o.shape[0] for o in out] == g['counts'].tolist()
     flat = torch.cat(out, 0).numpy() if sum(g['counts']) else np.zeros((0, 6), np.float32)
     assert np.array_equal(flat, g['dets'])
+
+
+def per_class_nms(pred_b, nc, kw):
+    """NMS of every class on its own (no interaction between classes possible), merged by confidence."""
+    parts = [non_max_suppression_ref(pred_b, classes=[c], **{**kw, 'max_det': 4096})[0] for c in range(nc)]
+    u = torch.cat(parts, 0)
+    return u[u[:, 4].argsort(descending=True, stable=True)][:kw.get('max_det', 300)]
+
+
+@pytest.mark.parametrize('case', WIDE_CASES, ids=[c[0] for c in WIDE_CASES])
+def test_nms_ref_cross_class_suppression_golden(case, gold):
+    """Boxes larger than 4096 px: the class offset of general.py:702-704 no longer separates neighbouring classes.
+    The oracle must reproduce the real reference, and the case must not be vacuous: the reference result has to
+    DIFFER from class-by-class NMS (= at least one suppression crossed classes)."""
+    tag, B, A, nc, seed, mixed, kw = case
+    g = gold(f'nms_{tag}.npz')
+    pred = synth_pred_wide(B, A, nc, seed=seed, mixed=mixed)
+    out = non_max_suppression_ref(pred, **kw)
+    assert [o.shape[0] for o in out] == g['counts'].tolist()
+    assert np.array_equal(torch.cat(out, 0).numpy(), g['dets'])
+    for b in range(B):
+        indep = per_class_nms(pred[b:b + 1], nc, kw)
+        assert indep.shape[0] > out[b].shape[0], 'no suppression crossed classes: the case is vacuous'
+    if mixed:     # the first 256-candidate chunks of the sorted order are narrow boxes (extent < 4000 px), wide ones follow
+        x = pred[0]
+        conf = x[:, 4] * x[:, 5:].max(1)[0]
+        order = conf.argsort(descending=True)
+        wide = x[order, 2] > 1000
+        assert not bool(wide[:1024].any()) and bool(wide[1024:].any())
 
 
 def test_nms_ref_max_det_param_consistent():

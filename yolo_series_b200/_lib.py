@@ -20,7 +20,7 @@ EXPORTS = [
     'yb_conv_plan_destroy', 'yb_maxpool2x2', 'yb_maxpool_s1', 'yb_spp3',
     'yb_upsample2x', 'yb_copy', 'yb_add', 'yb_stage_input', 'yb_stem_conv', 'yb_decode', 'yb_nms_workspace_bytes',
     'yb_nms', 'yb_decode_nms', 'yb_engine_create', 'yb_engine_forward', 'yb_engine_num_launches', 'yb_engine_profile',
-    'yb_engine_destroy', 'yb_letterbox', 'yb_scale_coords', 'yb_scale_img', 'yb_decode_tta', 'yb_box_iou',
+    'yb_engine_op_kernel', 'yb_engine_destroy', 'yb_letterbox', 'yb_scale_coords', 'yb_scale_img', 'yb_decode_tta', 'yb_box_iou',
     'yb_match_detections', 'yb_decode_nms_gather', 'yb_peer_wait', 'yb_peer_alloc', 'yb_peer_open', 'yb_peer_close',
     'yb_peer_free',
 ]
@@ -89,6 +89,8 @@ def lib():
     L.yb_engine_destroy.argtypes = [C.c_void_p]
     L.yb_engine_forward.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     L.yb_engine_num_launches.argtypes = [C.c_void_p]
+    L.yb_engine_op_kernel.argtypes = [C.c_void_p, C.c_int]
+    L.yb_engine_op_kernel.restype = C.c_char_p
     L.yb_engine_profile.argtypes = [C.c_void_p, C.POINTER(C.c_float), C.c_void_p]
     L.yb_conv2d.argtypes = [C.POINTER(ConvDesc), C.c_void_p]
     L.yb_conv_plan_create.argtypes = [C.POINTER(ConvDesc), C.POINTER(C.c_void_p)]
@@ -128,12 +130,12 @@ def lib():
                                        C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                        C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.POINTER(PeerGatherC), C.c_void_p]
-    L.yb_peer_wait.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p]
+    L.yb_peer_wait.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_uint, C.c_void_p]
     L.yb_peer_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]
     L.yb_peer_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
     L.yb_peer_close.argtypes = [C.c_void_p]
     L.yb_peer_free.argtypes = [C.c_void_p]
-    if L.yb_abi_version() != 1:
+    if L.yb_abi_version() != 2:
         raise RuntimeError('libyolo_b200.so ABI version mismatch; rebuild')
     _lib = L
     return L
@@ -152,11 +154,18 @@ def torch_dtype_code(t):
 
 def view(t, c_off=0, C_=None):
     """Describe a contiguous NHWC torch tensor (N,H,W,Cbuf) or a channel slice of it."""
+    import torch
+    if t.device.type != 'cuda' or t.device.index != torch.cuda.current_device():
+        raise RuntimeError(f'tensor on {t.device} but the current CUDA device is cuda:{torch.cuda.current_device()}: '
+                           f'libyolo_b200 launches on the current device -- wrap the call in torch.cuda.device(...)')
     n, h, w, cb = t.shape
     c = cb - c_off if C_ is None else C_
     return Tensor(t.data_ptr() + c_off * t.element_size(), torch_dtype_code(t.dtype), n, h, w, c, cb)
 
 
-def stream_ptr():
+def stream_ptr(device=None):
+    """Current CUDA stream of ``device`` (default: the current device).  Every C entry point launches on the CURRENT
+    device, so callers that hold tensors of a specific device wrap the call in ``torch.cuda.device(dev)`` (Engine,
+    nms._run_nms, preprocess, evaluate do) -- a model on cuda:1 must not launch on cuda:0."""
     import torch
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)

@@ -163,6 +163,27 @@ extern "C" int yb_engine_profile(yb_engine* e, float* ms_per_op, void* stream) {
 
 extern "C" int yb_engine_num_launches(const yb_engine* e) { return e ? e->launches : 0; }
 
+extern "C" const char* yb_engine_op_kernel(const yb_engine* e, int i) {
+  if (!e || i < 0 || i >= (int)e->ops.size()) return nullptr;
+  const yb_op& o = e->ops[i];
+  switch (o.kind) {
+    case YB_OP_CONV:
+      return e->plans_s2p[i] ? "k_conv3s2p_tc" : e->plans3[i] ? "k_conv3_tc" : e->plans[i] ? "k_conv_tc" : "k_conv_fp32";
+    case YB_OP_STEM: {
+      const yb_tensor& im = e->tensors[o.in0];
+      const yb_tensor& y = e->tensors[o.out0];
+      const bool tc = !o.tile_n && im.C == 3 && y.C == 32 && im.W % 4 == 0 && (uintptr_t)im.data % 16 == 0;
+      return tc ? "k_stem_tc" : "k_stem";
+    }
+    case YB_OP_MAXPOOL2: return "k_maxpool2";
+    case YB_OP_POOL_S1: return "k_pool_s1";
+    case YB_OP_SPP3: return "k_spp3";
+    case YB_OP_UPSAMPLE2: return "k_upsample2";
+    case YB_OP_COPY: case YB_OP_ADD: return "k_copy_add";
+    default: return "?";
+  }
+}
+
 extern "C" void yb_engine_destroy(yb_engine* e) {
   if (!e) return;
   for (auto* p : e->plans) conv_tc_plan_destroy(p);

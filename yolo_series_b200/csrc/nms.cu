@@ -1128,8 +1128,10 @@ __global__ void __launch_bounds__(kSortThreads, 1) k_sort_nms(const NmsParams P)
 }
 
 // One warp: lane r spins on this rank's arrival flag of rank r until it reaches `step` (acquire, system scope).
-// A bounded spin (~4 s of globaltimer) reports through *status instead of hanging the device.
-__global__ void k_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, int* status) {
+// A bounded spin (timeout_ns of globaltimer) reports through *status instead of hanging the device, and poisons the
+// late sender's block of the receive buffer (counts = -1) so that stale rows can never be read as detections.
+__global__ void k_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, int* status, int* counts, int B,
+                            unsigned long long timeout_ns) {
   const int r = threadIdx.x;
   if (r >= n_peers) return;
   unsigned long long t0, t1;
@@ -1139,7 +1141,11 @@ __global__ void k_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, i
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + r) : "memory");
     if ((int32_t)(v - step) >= 0) break;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
-    if (t1 - t0 > 4000000000ull) { if (status) atomicOr(status, 1 << 8); break; }
+    if (t1 - t0 > timeout_ns) {
+      if (status) atomicOr(status, 1 << 8);
+      if (counts) for (int i = 0; i < B; ++i) counts[r * B + i] = -1;
+      break;
+    }
     __nanosleep(200);
   }
 }
@@ -1402,9 +1408,12 @@ extern "C" int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no
                               max_det, cand_cap, workspace, workspace_bytes, out, counts, overflow, nullptr, stream);
 }
 
-extern "C" int yb_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, int* status, void* stream) {
-  YB_CHECK_ARG(flags && n_peers > 0 && n_peers <= YB_MAX_PEERS && n_peers <= 32, "yb_peer_wait: bad arguments");
-  k_peer_wait<<<1, 32, 0, (cudaStream_t)stream>>>(flags, n_peers, step, status);
+extern "C" int yb_peer_wait(const uint32_t* flags, int n_peers, uint32_t step, int* status, int32_t* counts, int B,
+                            unsigned timeout_ms, void* stream) {
+  YB_CHECK_ARG(flags && n_peers > 0 && n_peers <= YB_MAX_PEERS && n_peers <= 32 && (!counts || B > 0),
+               "yb_peer_wait: bad arguments");
+  const unsigned long long ns = (unsigned long long)(timeout_ms ? timeout_ms : 20000u) * 1000000ull;
+  k_peer_wait<<<1, 32, 0, (cudaStream_t)stream>>>(flags, n_peers, step, status, counts, B, ns);
   YB_LAUNCH_CHECK();
   return YB_OK;
 }

@@ -57,8 +57,12 @@ class PeerGather:
     compute stream, so nobody overwrites a set that is still being read.
     """
 
-    def __init__(self, B, max_det, group=None, device=None):
+    def __init__(self, B, max_det, group=None, device=None, timeout_s=None):
+        """``timeout_s`` (default: env YB_PEER_TIMEOUT_S or 20): how long ``finish`` waits for a peer before it poisons that
+        peer's block (counts = -1) and sets the status word; ``Model.detect`` / ``detect_batches`` raise on a poisoned
+        block wherever they already read the counts back."""
         import ctypes as C
+        import os
 
         from . import _lib
         if not (dist.is_available() and dist.is_initialized()):
@@ -68,6 +72,7 @@ class PeerGather:
         if self.world > _lib.MAX_PEERS:
             raise ValueError(f'PeerGather supports up to {_lib.MAX_PEERS} GPUs of one box')
         self.B, self.max_det = int(B), int(max_det)
+        self.timeout_ms = int(1000 * float(timeout_s if timeout_s is not None else os.environ.get('YB_PEER_TIMEOUT_S', 20)))
         self.device = device if device is not None else torch.device('cuda', torch.cuda.current_device())
         self.lib = _lib.lib()
         w = self.world
@@ -161,10 +166,22 @@ class PeerGather:
         import ctypes as C
 
         from . import _lib
-        _lib.check(self.lib.yb_peer_wait(C.c_void_p(self.local + self.off_flag[slot]), self.world, step,
-                                         C.c_void_p(self.status.data_ptr()), _lib.stream_ptr()), 'yb_peer_wait')
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.yb_peer_wait(C.c_void_p(self.local + self.off_flag[slot]), self.world, step,
+                                             C.c_void_p(self.status.data_ptr()),
+                                             C.c_void_p(self.local + self.off_cnt[slot]), self.B, self.timeout_ms,
+                                             _lib.stream_ptr()), 'yb_peer_wait')
         out, cnt = self._views[slot]
         return out.clone(), cnt.clone()
+
+    @staticmethod
+    def raise_if_poisoned(counts_host):
+        """``counts_host``: the gathered per-image counts after a host read-back.  A block whose sender did not arrive in
+        time carries -1 (k_peer_wait) -- never return it as detections."""
+        if bool((counts_host < 0).any()):
+            late = sorted({int(i) for i in (counts_host < 0).nonzero().flatten().tolist()})
+            raise RuntimeError(f'PeerGather: timed out waiting for a peer rank (images {late[:4]}... carry no data); '
+                               f'raise YB_PEER_TIMEOUT_S or check the slow rank')
 
     def check(self):
         """One 4-byte read-back: raises if a wait timed out (a peer never arrived)."""

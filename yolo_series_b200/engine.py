@@ -20,9 +20,16 @@ def _round_up(x, m):
 
 class Engine:
     def __init__(self, lowered, B, H, W, device, dtype=torch.bfloat16, use_graph=True, tile_overrides=None,
-                 img_dtype=torch.uint8, fuse_stem=True):
+                 img_dtype=torch.uint8, fuse_stem=True, packed=None):
         if device.type != 'cuda':
             raise RuntimeError('yolo_series_b200 runs on CUDA (sm_100a) only; there is no CPU fallback')
+        if device.index is None:
+            device = torch.device('cuda', torch.cuda.current_device())
+        # every C entry point launches on the CURRENT device: pin it to the engine's device for all calls
+        with torch.cuda.device(device):
+            self._build(lowered, B, H, W, device, dtype, use_graph, tile_overrides, img_dtype, fuse_stem, packed)
+
+    def _build(self, lowered, B, H, W, device, dtype, use_graph, tile_overrides, img_dtype, fuse_stem, packed):
         self.L, self.B, self.H, self.W = lowered, B, H, W
         self.device, self.dtype, self.use_graph = device, dtype, use_graph
         self.lib = _lib.lib()
@@ -93,10 +100,18 @@ class Engine:
                 cin_pad = max(_round_up(fc.c_in, 8 if dtype == torch.bfloat16 else 4), xin.C)
                 if dtype == torch.bfloat16:
                     cin_pad = max(cin_pad, 16)
-                w = torch.zeros((fc.c_out, fc.k * fc.k, cin_pad), dtype=torch.float32)
-                w[:, :, :fc.c_in] = fc.weight.permute(0, 2, 3, 1).reshape(fc.c_out, fc.k * fc.k, fc.c_in)
-                wd = w.to(device=device, dtype=dtype).contiguous()
-                bd = fc.bias.to(device=device, dtype=torch.float32).contiguous()
+                # packed weights do not depend on the input shape: engines of one model share them (`packed` is the
+                # model's cache, keyed by op name / padding / dtype / device)
+                pk = (op.name, cin_pad, dtype, str(device))
+                if packed is not None and pk in packed:
+                    wd, bd = packed[pk]
+                else:
+                    w = torch.zeros((fc.c_out, fc.k * fc.k, cin_pad), dtype=torch.float32)
+                    w[:, :, :fc.c_in] = fc.weight.permute(0, 2, 3, 1).reshape(fc.c_out, fc.k * fc.k, fc.c_in)
+                    wd = w.to(device=device, dtype=dtype).contiguous()
+                    bd = fc.bias.to(device=device, dtype=torch.float32).contiguous()
+                    if packed is not None:
+                        packed[pk] = (wd, bd)
                 self.weights.append(wd)
                 self.biases.append(bd)
                 o.weight = len(self.weights) - 1
@@ -142,7 +157,8 @@ class Engine:
             if img.dtype != self.img_dtype or tuple(img.shape) != tuple(self.img_buf.shape):
                 raise ValueError(f'engine built for {tuple(self.img_buf.shape)} {self.img_dtype}, got '
                                  f'{tuple(img.shape)} {img.dtype}')
-            self.img_buf.copy_(img, non_blocking=True)     # D2D, or H2D straight from (pinned) host memory
+            with torch.cuda.device(self.device):
+                self.img_buf.copy_(img, non_blocking=True)     # D2D, or H2D straight from (pinned) host memory
             return
         if img.device != self.device:
             img = img.to(self.device, non_blocking=True)
@@ -151,17 +167,20 @@ class Engine:
         b, c, h, w = img.shape
         if (b, h, w) != (self.B, self.H, self.W):
             raise ValueError(f'engine built for {(self.B, self.H, self.W)}, got {(b, h, w)}')
-        _lib.check(self.lib.yb_stage_input(C.c_void_p(img.data_ptr()), code, b, c, h, w, int(self.L.reorg),
-                                           C.byref(self.input_view), _lib.stream_ptr()), 'yb_stage_input')
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.yb_stage_input(C.c_void_p(img.data_ptr()), code, b, c, h, w, int(self.L.reorg),
+                                               C.byref(self.input_view), _lib.stream_ptr()), 'yb_stage_input')
 
     def run(self):
-        _lib.check(self.lib.yb_engine_forward(self.handle, int(self.use_graph), _lib.stream_ptr()),
-                   'yb_engine_forward')
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.yb_engine_forward(self.handle, int(self.use_graph), _lib.stream_ptr()),
+                       'yb_engine_forward')
 
     def profile(self):
         """Per-op device time (ms) of one eager pass, with op descriptions: [(name, kind, ms, flops)]."""
         ms = (C.c_float * self.n_ops)()
-        _lib.check(self.lib.yb_engine_profile(self.handle, ms, _lib.stream_ptr()), 'yb_engine_profile')
+        with torch.cuda.device(self.device):
+            _lib.check(self.lib.yb_engine_profile(self.handle, ms, _lib.stream_ptr()), 'yb_engine_profile')
         rows = []
         for i, op in enumerate(self.L.ops):
             fl = 0
@@ -174,14 +193,51 @@ class Engine:
             rows.append((op.name, op.kind, float(ms[i]), fl))
         return rows
 
+    def op_kernel(self, i):
+        """Name of the CUDA kernel op ``i`` launches (yb_engine_op_kernel)."""
+        n = self.lib.yb_engine_op_kernel(self.handle, i)
+        return n.decode() if n else '?'
+
+    def op_bytes(self, i):
+        """Algorithmic HBM bytes of op ``i``: every input and output element once, weights once."""
+        op = self.L.ops[i]
+
+        def vb(v, c=None):
+            return v.N * v.H * v.W * (v.C if c is None else c) * {YB_F32: 4, YB_BF16: 2, YB_U8: 1}[v.dtype]
+        total = sum(vb(self.views[o]) for o in op.outs)
+        if op.kind == OP_CONV and self.img_buf is not None and self.L.input_val in op.ins:     # fused stem reads the raw image
+            total += self.img_buf.numel() * self.img_buf.element_size()
+        else:
+            total += sum(vb(self.views[v]) for v in op.ins)
+        if op.kind == OP_CONV:
+            fc = op.conv
+            total += fc.c_out * fc.k * fc.k * fc.c_in * (2 if self.dtype == torch.bfloat16 else 4) + fc.c_out * 4
+        return total
+
+    def profile_table(self, reps=3):
+        """[{op, kernel, ms, flops, bytes}] -- per-op device time of an eager pass (median of ``reps``)."""
+        runs = [self.profile() for _ in range(reps)]
+        rows = []
+        for i, r in enumerate(runs[0]):
+            ms = sorted(run[i][2] for run in runs)[reps // 2]
+            rows.append({'op': r[0], 'kernel': self.op_kernel(i), 'ms': ms, 'flops': r[3], 'bytes': self.op_bytes(i)})
+        return rows
+
     def num_launches(self):
         return self.lib.yb_engine_num_launches(self.handle)
 
-    def __del__(self):
+    def destroy(self):
+        """Free the C-side plans / graph now (the HBM buffers go when the last Python reference does)."""
         h = getattr(self, 'handle', None)
         if h:
             try:
-                self.lib.yb_engine_destroy(h)
+                with torch.cuda.device(self.device):
+                    torch.cuda.synchronize(self.device)       # a replay may still be in flight
+                    self.lib.yb_engine_destroy(h)
             except Exception:
                 pass
             self.handle = None
+        self.buffers, self.views, self.head = {}, [], []
+
+    def __del__(self):
+        self.destroy()

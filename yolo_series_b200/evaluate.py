@@ -37,9 +37,10 @@ def box_iou(box1, box2):
         b2 = b2.contiguous()
     n, m = b1.shape[0], b2.shape[0]
     out = torch.empty((n, m), dtype=torch.float32, device=b1.device)
-    _lib.check(_lib.lib().yb_box_iou(C.c_void_p(b1.data_ptr()), n, b1.stride(0) if n > 1 else 4,
-                                     C.c_void_p(b2.data_ptr()), m, b2.stride(0) if m > 1 else 4,
-                                     C.c_void_p(out.data_ptr()), _lib.stream_ptr()), 'yb_box_iou')
+    with torch.cuda.device(b1.device):
+        _lib.check(_lib.lib().yb_box_iou(C.c_void_p(b1.data_ptr()), n, b1.stride(0) if n > 1 else 4,
+                                         C.c_void_p(b2.data_ptr()), m, b2.stride(0) if m > 1 else 4,
+                                         C.c_void_p(out.data_ptr()), _lib.stream_ptr()), 'yb_box_iou')
     return out if box1.dtype == torch.float32 else out.to(box1.dtype)
 
 
@@ -67,11 +68,12 @@ def match_batch(out, counts, targets, img1_shape, metas, iouv, use_ratio_pad=Tru
     correct = torch.empty((B, max_det, niou), dtype=torch.uint8, device=dev)
     detected = torch.zeros(max(T, 1), dtype=torch.uint8, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
-    _lib.check(_lib.lib().yb_match_detections(C.c_void_p(out.data_ptr()), C.c_void_p(counts.data_ptr()), B, max_det,
-                                              C.c_void_p(targets.data_ptr()) if T else None, T,
-                                              C.c_void_p(tab.data_ptr()), C.c_void_p(iouv.data_ptr()), niou,
-                                              C.c_void_p(correct.data_ptr()), C.c_void_p(detected.data_ptr()),
-                                              C.c_void_p(status.data_ptr()), _lib.stream_ptr()), 'yb_match_detections')
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().yb_match_detections(C.c_void_p(out.data_ptr()), C.c_void_p(counts.data_ptr()), B, max_det,
+                                                  C.c_void_p(targets.data_ptr()) if T else None, T,
+                                                  C.c_void_p(tab.data_ptr()), C.c_void_p(iouv.data_ptr()), niou,
+                                                  C.c_void_p(correct.data_ptr()), C.c_void_p(detected.data_ptr()),
+                                                  C.c_void_p(status.data_ptr()), _lib.stream_ptr()), 'yb_match_detections')
     correct = correct.bool()
     correct._yb_status = status           # read with check_match_status() after the caller's own synchronisation
     return (correct, detected[:T].bool()) if return_detected else correct

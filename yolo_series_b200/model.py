@@ -13,6 +13,7 @@ Same constructor ``Model(cfg, ch=3, nc=None, anchors=None)`` (yolo.py:509), same
 import ctypes as C
 import math
 import os
+from collections import OrderedDict
 from copy import deepcopy
 
 import torch
@@ -45,51 +46,69 @@ def _resolve_arg(a, scope):
     return a  # e.g. 'nearest'
 
 
+def _sources(spec, index):
+    """Absolute producer indices of a cfg row's ``from`` field (negative = relative to ``index``)."""
+    refs = [spec] if isinstance(spec, int) else list(spec)
+    return [index + r if r < 0 else r for r in refs]
+
+
+# Channel rule per module family: (input widths, resolved args, head width, width multiple) -> (ctor args, Cout).
+# ``None`` as Cout means "no feature map" (the detection head ends the graph).
+def _rule_conv(cin, args, head_no, gw, repeats=None):
+    cout = args[0] if args[0] == head_no else make_divisible(args[0] * gw, 8)
+    ctor = [cin[0], cout] + ([] if repeats is None else [repeats]) + list(args[1:])
+    return ctor, cout
+
+
+def _rule_head(cin, args, head_no, gw):
+    ctor = list(args)
+    if isinstance(ctor[1], int):                       # anchors given as a count: placeholder values per level
+        ctor[1] = [list(range(ctor[1] * 2))] * len(cin)
+    return ctor + [list(cin)], None
+
+
+_CHANNEL_RULES = {
+    'Conv': _rule_conv, 'RepConv': _rule_conv,
+    'DownC': _rule_conv, 'SPPCSPC': _rule_conv,          # these two take the repeat count as their third argument
+    'Concat': lambda c, a, h, g: (list(a), sum(c)),
+    'Shortcut': lambda c, a, h, g: (list(a), c[0]),
+    'ReOrg': lambda c, a, h, g: (list(a), 4 * c[0]),
+    'Detect': _rule_head, 'IDetect': _rule_head, 'IAuxDetect': _rule_head,
+}
+_PASS_THROUGH = lambda c, a, h, g: (list(a), c[0])     # MP, SP, nn.Upsample: width unchanged
+
+
 def parse_model(d, ch):
     """cfg dict -> (nn.Sequential of parameter containers with .i/.f/.type/.np, save list).
-    Grammar: SURVEY.md A.3 / reference yolo.py:736-813."""
-    anchors, nc, gd, gw = d['anchors'], d['nc'], d['depth_multiple'], d['width_multiple']
-    na = (len(anchors[0]) // 2) if isinstance(anchors, list) else anchors
-    no = na * (nc + 5)
-    scope = {'nc': nc, 'anchors': anchors}
-    layers, save, c2 = [], [], ch[-1]
-    for i, (f, n, mname, args) in enumerate(d['backbone'] + d['head']):
-        if mname not in modules.REGISTRY:
-            raise NotImplementedError(f'cfg node {i}: module {mname!r} is outside the yolov7 hot path')
-        cls = modules.REGISTRY[mname]
-        args = [_resolve_arg(a, scope) for a in args]
-        n = max(round(n * gd), 1) if n > 1 else n
-        if mname in modules.CONV_LIKE:
-            c1, c2 = ch[f], args[0]
-            if c2 != no:
-                c2 = make_divisible(c2 * gw, 8)
-            args = [c1, c2, *args[1:]]
-            if mname in ('DownC', 'SPPCSPC'):
-                args.insert(2, n)
-                n = 1
-        elif mname == 'Concat':
-            c2 = sum(ch[x] for x in f)
-        elif mname == 'Shortcut':
-            c2 = ch[f[0]]
-        elif mname in ('Detect', 'IDetect', 'IAuxDetect'):
-            args.append([ch[x] for x in f])
-            if isinstance(args[1], int):
-                args[1] = [list(range(args[1] * 2))] * len(f)
-        elif mname == 'ReOrg':
-            c2 = ch[f] * 4
-        else:
-            c2 = ch[f]
-        if n != 1:
+    Same grammar as the reference's builder (yolo.py:736-813), driven by ``_CHANNEL_RULES``
+    instead of an if-chain; ``eval()`` of cfg strings is replaced by ``_resolve_arg`` + ``modules.REGISTRY``."""
+    anchors = d['anchors']
+    per_level = (len(anchors[0]) // 2) if isinstance(anchors, list) else anchors
+    head_no = per_level * (d['nc'] + 5)
+    gd, gw = d['depth_multiple'], d['width_multiple']
+    names = {'nc': d['nc'], 'anchors': anchors}
+    rows = list(d['backbone']) + list(d['head'])
+    widths, nodes, kept = [], [], set()
+    for index, (spec, repeats, mname, raw_args) in enumerate(rows):
+        cls = modules.REGISTRY.get(mname)
+        if cls is None:
+            raise NotImplementedError(f'cfg node {index}: module {mname!r} is outside the yolov7 hot path')
+        depth = max(round(repeats * gd), 1) if repeats > 1 else repeats
+        takes_depth = mname in ('DownC', 'SPPCSPC')
+        if depth != 1 and not takes_depth:
             raise NotImplementedError('depth repeats > 1 do not occur in the yolov7 cfgs')
-        m_ = cls(*args)
-        m_.i, m_.f, m_.type = i, f, mname
-        m_.np = sum(x.numel() for x in m_.parameters())
-        save.extend(x % i for x in ([f] if isinstance(f, int) else f) if x != -1)
-        layers.append(m_)
-        if i == 0:
-            ch = []
-        ch.append(c2)
-    return nn.Sequential(*layers), sorted(save)
+        srcs = _sources(spec, index)
+        cin = [ch[-1]] if index == 0 else [widths[j] for j in srcs]
+        rule = _CHANNEL_RULES.get(mname, _PASS_THROUGH)
+        resolved = [_resolve_arg(a, names) for a in raw_args]
+        ctor, cout = rule(cin, resolved, head_no, gw, depth) if takes_depth else rule(cin, resolved, head_no, gw)
+        node = cls(*ctor)
+        node.i, node.f, node.type = index, spec, mname
+        node.np = sum(p.numel() for p in node.parameters())
+        kept.update(j for j, r in zip(srcs, [spec] if isinstance(spec, int) else spec) if r != -1)
+        nodes.append(node)
+        widths.append(cout)
+    return nn.Sequential(*nodes), sorted(kept)
 
 
 def _node_strides(layers):
@@ -149,7 +168,7 @@ class Model(nn.Module):
             if isinstance(m, nn.BatchNorm2d):     # utils/torch_utils.py:150-151
                 m.eps, m.momentum = 1e-3, 0.03
         self._fused = False
-        self._engines = {}
+        self._engines, self._packed = OrderedDict(), {}
         self._compute_dtype = torch.bfloat16
         self.use_graph = True
 
@@ -197,8 +216,17 @@ class Model(nn.Module):
         self._invalidate()
         return out
 
+    # Engines are shape-specialised (buffers + TMA plans + CUDA graph: 5.5 GB at yolov7 / 640 / B=32) and the reference's
+    # callers produce many shapes (test.py rect batches, detect.py streams, the short last batch, 3 TTA scales), so
+    # the cache is a small LRU; evicted engines are destroyed at once.  Packed weights are shape-independent and are
+    # shared by all engines of the model (`_packed`).
+    engine_cache_size = 6
+
     def _invalidate(self):
-        self._engines = {}
+        for e in getattr(self, '_engines', {}).values():
+            e.destroy()
+        self._engines = OrderedDict()
+        self._packed = {}
         self._lowered = None
 
     def info(self, verbose=False, img_size=640):
@@ -213,6 +241,8 @@ class Model(nn.Module):
         return False
 
     def _get_engine(self, B, H, W, device, img_dtype=torch.uint8):
+        if device.index is None:
+            device = torch.device('cuda', torch.cuda.current_device())
         key = (B, H, W, str(device), self._compute_dtype, img_dtype)
         eng = self._engines.get(key)
         if eng is None:
@@ -220,10 +250,17 @@ class Model(nn.Module):
                 with torch.no_grad():
                     self._lowered = plan.lower(self._layers(), in_ch=self.yaml.get('ch', 3),
                                                fused=self._is_ref_fused())
+            while len(self._engines) >= max(1, int(self.engine_cache_size)):
+                _, old = self._engines.popitem(last=False)       # least recently used
+                old.destroy()
+            if not hasattr(self, '_packed'):
+                self._packed = {}
             eng = Engine(self._lowered, B, H, W, device, self._compute_dtype, self.use_graph,
                          getattr(self, 'tile_overrides', None), img_dtype=img_dtype,
-                         fuse_stem=getattr(self, 'fuse_stem', True))
+                         fuse_stem=getattr(self, 'fuse_stem', True), packed=self._packed)
             self._engines[key] = eng
+        else:
+            self._engines.move_to_end(key)
         return eng
 
     def _device(self):
@@ -298,9 +335,10 @@ class Model(nn.Module):
         B, Cc, H, W = x.shape
         out = torch.empty((B, Cc, HW[0], HW[1]), dtype=torch.float32, device=dev)
         code = _lib.YB_U8 if x.dtype == torch.uint8 else _lib.YB_F32
-        _lib.check(_lib.lib().yb_scale_img(C.c_void_p(x.data_ptr()), code, B, Cc, H, W, int(fi or 0), hw[0], hw[1],
-                                           C.c_void_p(out.data_ptr()), HW[0], HW[1], 0.447, _lib.stream_ptr()),
-                   'yb_scale_img')
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().yb_scale_img(C.c_void_p(x.data_ptr()), code, B, Cc, H, W, int(fi or 0), hw[0], hw[1],
+                                               C.c_void_p(out.data_ptr()), HW[0], HW[1], 0.447, _lib.stream_ptr()),
+                       'yb_scale_img')
         return out
 
     def forward_into(self, x, pred, row_off, augment=False):
@@ -317,10 +355,22 @@ class Model(nn.Module):
             lv, head = self.head_levels(eng)
             A = sum(head.na * v.H * v.W for v in eng.head_views)
             tp = _lib.TtaPass(pred.shape[1], row_off + written, float(si), int(fi or 0), float(H), float(W))
-            _lib.check(eng.lib.yb_decode_tta(lv, head.nl, head.na, head.no, C.c_void_p(pred.data_ptr()), C.byref(tp),
-                                             _lib.stream_ptr()), 'yb_decode_tta')
+            with torch.cuda.device(eng.device):
+                _lib.check(eng.lib.yb_decode_tta(lv, head.nl, head.na, head.no, C.c_void_p(pred.data_ptr()), C.byref(tp),
+                                                 _lib.stream_ptr()), 'yb_decode_tta')
             written += A
         return written
+
+    def _print_profile(self, eng):
+        """``model(x, profile=True)`` (yolo.py:614-623, 629-630): the reference prints GFLOPS / params / ms per node and
+        the total; here the unit of execution is the lowered op (one kernel launch), timed with CUDA events."""
+        rows = eng.profile_table(3)
+        print(f"{'ms':>9s} {'GFLOP':>9s} {'TFLOP/s':>8s} {'GB/s':>7s}  {'kernel':<16s} op")
+        for r in rows:
+            print(f"{r['ms']:9.4f} {r['flops'] / 1e9:9.2f} {r['flops'] / r['ms'] / 1e9 if r['flops'] else 0:8.1f} "
+                  f"{r['bytes'] / r['ms'] / 1e6:7.0f}  {r['kernel']:<16s} {r['op']}")
+        print(f"{sum(r['ms'] for r in rows):.3f} ms total (eager, one event per op), "
+              f"{sum(r['flops'] for r in rows) / 1e9:.1f} GFLOP, batch {eng.B}")
 
     @torch.no_grad()
     def forward(self, x, augment=False, profile=False):
@@ -339,8 +389,11 @@ class Model(nn.Module):
         raws = [torch.empty((eng.B, head.na, v.H, v.W, head.no), dtype=torch.float32, device=eng.device)
                 for v in eng.head_views]
         raw_ptrs = (C.c_void_p * head.nl)(*[r.data_ptr() for r in raws])
-        _lib.check(eng.lib.yb_decode(lv, head.nl, head.na, head.no, C.c_void_p(pred.data_ptr()), raw_ptrs,
-                                     _lib.stream_ptr()), 'yb_decode')
+        with torch.cuda.device(eng.device):
+            _lib.check(eng.lib.yb_decode(lv, head.nl, head.na, head.no, C.c_void_p(pred.data_ptr()), raw_ptrs,
+                                         _lib.stream_ptr()), 'yb_decode')
+        if profile:
+            self._print_profile(eng)
         return pred, raws
 
     @torch.no_grad()
@@ -364,6 +417,14 @@ class Model(nn.Module):
         lv, head = self.head_levels(eng)
         A = sum(head.na * v.H * v.W for v in eng.head_views)
         if gather is not None:
+            if getattr(eng, '_gather_warmed', None) is not gather:
+                # first use of this engine: lowering, weight packing, TMA plans and graph capture just happened inside
+                # run_trunk and take seconds -- line the ranks up before the first exchange so that nobody's bounded
+                # wait starts while a peer is still building
+                import torch.distributed as tdist
+                torch.cuda.synchronize(eng.device)
+                tdist.barrier(group=gather.group)
+                eng._gather_warmed = gather
             table, slot, step = gather.begin(eng.B, max_det)
             out, meta = _run_nms(None, eng.B, A, head.no, conf_thres, iou_thres, classes, agnostic, multi_label, max_nms,
                                  max_det, eng.device, levels=(lv, head.nl, head.na), return_packed=True, peer=table)
@@ -372,6 +433,7 @@ class Model(nn.Module):
             if packed:
                 return out_all, meta_all
             host = meta_all.cpu()
+            gather.raise_if_poisoned(host[:-1])
             if int(host[-1]) != 0:
                 raise RuntimeError('yb_nms: candidate capacity exceeded (YB_ERR_OVERFLOW)')
             return [out_all[i, :int(host[i])] for i in range(out_all.shape[0])]
@@ -408,6 +470,8 @@ class Model(nn.Module):
             B = meta.numel() - 1
             if int(meta[B]) != 0:
                 raise RuntimeError('yb_nms: candidate capacity exceeded (YB_ERR_OVERFLOW)')
+            if gather is not None:
+                gather.raise_if_poisoned(meta[:B])
             s['keep'] = None
             return s['host'][0], meta[:B]
 
@@ -458,7 +522,7 @@ class AcceleratedModel(Model):
         self.save = getattr(ref_model, 'save', [])
         self.names = getattr(ref_model, 'names', None)
         self.stride = ref_model.stride
-        self._engines, self._lowered = {}, None
+        self._engines, self._packed, self._lowered = OrderedDict(), {}, None
         self._compute_dtype = torch.bfloat16
         self.use_graph = True
 

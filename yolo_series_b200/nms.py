@@ -42,17 +42,18 @@ def _run_nms(pred, B, A, no, conf_thres, iou_thres, classes, agnostic, multi_lab
     common = (C.c_float(conf_thres), C.c_double(iou_thres), cls_arr, n_cls, int(bool(agnostic)),
               int(bool(multi_label)), int(max_nms), int(max_det), int(cand_cap), C.c_void_p(ws_ptr), ws_len,
               C.c_void_p(out.data_ptr()), C.c_void_p(meta.data_ptr()), C.c_void_p(meta.data_ptr() + 4 * B))
-    if levels is None:
-        if peer is not None:
-            raise ValueError('the peer gather is fused into yb_decode_nms_gather (Model.detect), not the stand-alone yb_nms')
-        _lib.check(L.yb_nms(C.c_void_p(pred.data_ptr()), B, A, no, *common, _lib.stream_ptr()), 'yb_nms')
-    elif peer is not None:
-        lv, nl, na = levels
-        _lib.check(L.yb_decode_nms_gather(lv, nl, na, no, *common, C.byref(peer), _lib.stream_ptr()),
-                   'yb_decode_nms_gather')
-    else:
-        lv, nl, na = levels
-        _lib.check(L.yb_decode_nms(lv, nl, na, no, *common, _lib.stream_ptr()), 'yb_decode_nms')
+    if levels is None and peer is not None:
+        raise ValueError('the peer gather is fused into yb_decode_nms_gather (Model.detect), not the stand-alone yb_nms')
+    with torch.cuda.device(device):          # the C side launches on the current device
+        if levels is None:
+            _lib.check(L.yb_nms(C.c_void_p(pred.data_ptr()), B, A, no, *common, _lib.stream_ptr()), 'yb_nms')
+        elif peer is not None:
+            lv, nl, na = levels
+            _lib.check(L.yb_decode_nms_gather(lv, nl, na, no, *common, C.byref(peer), _lib.stream_ptr()),
+                       'yb_decode_nms_gather')
+        else:
+            lv, nl, na = levels
+            _lib.check(L.yb_decode_nms(lv, nl, na, no, *common, _lib.stream_ptr()), 'yb_decode_nms')
     if return_packed:
         return out, meta
     host = meta.cpu()   # the single device->host read of the call (B+1 ints)

@@ -75,8 +75,9 @@ def _launch(frames, geos, out, layout, swap_rb, color):
         s.new_w, s.new_h, s.top, s.left = g['new_w'], g['new_h'], g['top'], g['left']
     border = (C.c_uint8 * 3)(*[int(c) & 255 for c in color])
     H, W = (out.shape[2], out.shape[3]) if layout == _lib.LAYOUT_CHW else (out.shape[1], out.shape[2])
-    _lib.check(_lib.lib().yb_letterbox(srcs, B, C.c_void_p(out.data_ptr()), H, W, layout, int(bool(swap_rb)), border,
-                                       _lib.stream_ptr()), 'yb_letterbox')
+    with torch.cuda.device(out.device):       # launches follow the tensors' device, like torch ops
+        _lib.check(_lib.lib().yb_letterbox(srcs, B, C.c_void_p(out.data_ptr()), H, W, layout, int(bool(swap_rb)), border,
+                                           _lib.stream_ptr()), 'yb_letterbox')
 
 
 def letterbox(img, new_shape=(640, 640), color=(114, 114, 114), auto=True, scaleFill=False, scaleup=True, stride=32):
@@ -125,9 +126,10 @@ def _scale(dets, B, max_rows, counts, table, do_round):
     tab = torch.tensor(table, dtype=torch.float32).to(dets.device, non_blocking=True)
     row_stride = dets.stride(-2)
     cptr = C.c_void_p(counts.data_ptr()) if counts is not None else None
-    _lib.check(_lib.lib().yb_scale_coords(C.c_void_p(dets.data_ptr()), B, max_rows, row_stride, cptr,
-                                          C.c_void_p(tab.data_ptr()), int(bool(do_round)), _lib.stream_ptr()),
-               'yb_scale_coords')
+    with torch.cuda.device(dets.device):
+        _lib.check(_lib.lib().yb_scale_coords(C.c_void_p(dets.data_ptr()), B, max_rows, row_stride, cptr,
+                                              C.c_void_p(tab.data_ptr()), int(bool(do_round)), _lib.stream_ptr()),
+                   'yb_scale_coords')
 
 
 def scale_coords(img1_shape, coords, img0_shape, ratio_pad=None):

@@ -77,3 +77,37 @@ def synth_pred(B, A, nc, seed=0, p_obj=0.3, clusters=(40, 80), extent=640.0, box
             obj = obj + torch.arange(A).float() * 1e-9
         out[b, :, :2], out[b, :, 2:4], out[b, :, 4], out[b, :, 5:] = xy, wh, obj, cls
     return out
+
+
+def synth_pred_wide(B, A, nc, seed=0, mixed=False, extent=1280.0):
+    """Predictions whose boxes are 6 000-9 000 px wide AND tall (centres inside ``extent``, so x1 / y1 go negative):
+    the reference adds ``cls * 4096`` to all four coordinates (utils/general.py:702-704), so such boxes of
+    NEIGHBOURING classes overlap after the offset, i.e. suppression crosses classes (IoU ~0.05-0.2).
+    ``mixed``: half of the rows are narrow 40x90 boxes of classes 0-2 in 60 tight clusters with the highest scores
+    (several 256-candidate chunks of the sorted order, few survivors) and only the lower-scoring rows are wide -- the
+    x extent of what has been seen crosses 4 000 px in the middle of an image."""
+    g = torch.Generator().manual_seed(seed)
+    out = torch.empty((B, A, nc + 5))
+    for b in range(B):
+        x = torch.rand((A,), generator=g) * extent
+        y = torch.rand((A,), generator=g) * extent
+        w = torch.rand((A,), generator=g) * 3000.0 + 6000.0
+        h = torch.rand((A,), generator=g) * 3000.0 + 6000.0
+        obj = torch.rand((A,), generator=g) * 0.7 + 0.3
+        hot = torch.randint(0, nc, (A,), generator=g)
+        if mixed:
+            narrow = torch.rand((A,), generator=g) < 0.5
+            cxy = torch.rand((60, 2), generator=g) * extent
+            pick = torch.randint(0, 60, (A,), generator=g)
+            jit = torch.randn((A, 2), generator=g) * 2.0
+            x = torch.where(narrow, cxy[pick, 0] + jit[:, 0], x)
+            y = torch.where(narrow, cxy[pick, 1] + jit[:, 1], y)
+            w = torch.where(narrow, torch.rand((A,), generator=g) * 20.0 + 30.0, w)
+            h = torch.where(narrow, torch.rand((A,), generator=g) * 45.0 + 68.0, h)
+            obj = torch.where(narrow, obj * 0.4 + 0.6, obj * 0.5)       # narrow rows score higher than every wide row
+            hot = torch.where(narrow, torch.randint(0, min(3, nc), (A,), generator=g), hot)
+        cls = torch.rand((A, nc), generator=g) * 0.05
+        cls[torch.arange(A), hot] = torch.rand((A,), generator=g) * 0.1 + 0.9
+        obj = obj + torch.arange(A).float() * 1e-9
+        out[b, :, 0], out[b, :, 1], out[b, :, 2], out[b, :, 3], out[b, :, 4], out[b, :, 5:] = x, y, w, h, obj, cls
+    return out
