@@ -51,7 +51,10 @@ def xywh2xyxy(x):  # general.py:275-282
 
 @torch.no_grad()
 def non_max_suppression_ref(prediction, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False,
-                            multi_label=False, labels=(), max_det=300, max_nms=30000, stable_cut=True):
+                            multi_label=False, labels=(), max_det=300, max_nms=30000, stable_cut=True,
+                            early_exit=True):
+    """``early_exit=False`` makes the greedy step visit every candidate like torchvision.ops.nms does (same result; used
+    when this function is TIMED as the reference's CPU cost -- stopping at max_det is a shortcut the reference lacks)."""
     prediction = prediction.float().cpu()
     nc = prediction.shape[2] - 5                                   # :636
     xc = prediction[..., 4] > conf_thres                           # :637
@@ -91,7 +94,7 @@ def non_max_suppression_ref(prediction, conf_thres=0.25, iou_thres=0.45, classes
             x = x[order[:max_nms]]
         c = x[:, 5:6] * (0 if agnostic else max_wh)                # :702
         boxes, scores = x[:, :4] + c, x[:, 4]                      # :703
-        i = greedy_nms(boxes, scores, iou_thres, max_keep=max_det)  # :704
+        i = greedy_nms(boxes, scores, iou_thres, max_keep=max_det if early_exit else 0)  # :704
         if i.shape[0] > max_det:                                   # :705-706
             i = i[:max_det]
         output[xi] = x[i]                                          # :715

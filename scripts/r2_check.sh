@@ -1,0 +1,25 @@
+#!/bin/bash
+# Round-2 standard GPU check: all GPU suites (one process per file), smoke, the bench line with extras.
+mkdir -p gpurun_out; rm -f gpurun_out/parity_refsize.jsonl gpurun_out/summary.txt
+nvidia-smi --query-gpu=name,driver_version,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
+PT="python -m pytest -q -m gpu --timeout 600 --timeout-method=thread -p no:cacheprovider"
+for f in test_gpu_nms test_gpu_ops test_gpu_e2e test_gpu_pre test_gpu_tta test_gpu_eval test_gpu_fullsize test_gpu_refsize; do
+  timeout 900 $PT tests/$f.py > gpurun_out/$f.log 2>&1
+  echo "$f exit $? $(tail -n 1 gpurun_out/$f.log)" | tee -a gpurun_out/summary.txt
+done
+grep -h "Error\|FAILED\|assert" gpurun_out/test_gpu_*.log | head -40
+timeout 600 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?" | tee -a gpurun_out/summary.txt; tail -n 2 gpurun_out/smoke.log
+timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?" | tee -a gpurun_out/summary.txt
+tail -c 1500 gpurun_out/bench.err
+python - <<'PY'
+import json
+d = json.loads(open('gpurun_out/bench.json').read().strip().splitlines()[-1])
+print('value', round(d['value'], 1), 'ms/step', round(d['ms_per_step'], 4), 'e2e', round(d['e2e']['value'], 1), 'clocks', d['clocks'])
+r = d.get('roofline', {})
+print({k: r.get(k) for k in ('kernel', 'bound', 'achieved', 'frac', 'ms_per_step', 'frac_of_layer_bound', 'trunk_graph_ms', 'decode_nms_ms', 'eager_per_op_sum_ms', 'conv_tflops', 'conv_frac_of_sustained_bf16', 'step_frac_of_layer_bounds')})
+for k in d.get('roofline_kernels', []):
+    print(' ', k['kernel'], k['launches'], 'ms', k['ms'], k['bound'], k['achieved'], k['unit'], 'frac', k['frac'], 'of-layer-bound', k['frac_of_layer_bound'])
+print('nms_stress', d.get('nms_stress'))
+print('cpu_baseline', d.get('cpu_baseline'))
+PY
+cat gpurun_out/parity_refsize.jsonl 2>/dev/null

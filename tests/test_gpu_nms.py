@@ -169,3 +169,51 @@ def test_decode_matches_torch_and_fused_path():
     # and NMS keep rows are bit-exact vs the oracle when fed the same (GPU-decoded) tensor
     r = non_max_suppression_ref(pred.cpu(), 0.05, 0.5)
     assert np.array_equal(_flat(a), _flat(r))
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16], ids=['f32', 'bf16'])
+def test_fused_multi_label_filter_gate_is_exact(dtype):
+    """multi_label=True (test.py:126, general.py:679-681) through the fused path: k_filter_cells<ML> walks one row
+    per thread and skips classes below a per-row logit gate derived from conf_thres / obj.  The gate must never
+    drop a candidate: fused result == stand-alone NMS over the decoded pred (evaluates every class) == oracle, for
+    thresholds from 'almost everything passes' to 'almost nothing', logits placed right at the gate, saturated
+    and non-finite logits, and a class whitelist."""
+    from yolo_series_b200 import non_max_suppression, ops
+    from yolo_series_b200.nms import _run_nms
+    g = torch.Generator().manual_seed(3)
+    na, nc = 3, 80
+    no = nc + 5
+    strides = [8., 16., 32.]
+    ag = [[[12, 16], [19, 36], [40, 28]], [[36, 75], [76, 55], [72, 146]], [[142, 110], [192, 243], [459, 401]]]
+    B = 2
+    logits = [torch.randn((B, 32 // (2 ** i), 48 // (2 ** i), 256), generator=g) * 2.5 - 1 for i in range(3)]
+    # adversarial rows: class logits exactly at / one ulp around logit(thr / obj), huge and tiny logits, NaN / inf
+    t = logits[0]
+    t[0, 0, 0, 5:85] = 40.0
+    t[0, 0, 1, 5:85] = -40.0
+    t[0, 0, 2, 4] = 40.0                                   # obj == 1
+    t[0, 0, 3, 4] = float(torch.logit(torch.tensor(0.05)))  # obj right at a threshold used below
+    t[0, 0, 4, 7] = float('nan')
+    t[0, 0, 5, 9] = float('inf')
+    t[0, 0, 6, 11] = float('-inf')
+    for k, thr in enumerate((0.001, 0.05, 0.25)):           # logits at the exact gate of row (0, 1, k)
+        obj = torch.sigmoid(t[0, 1, k, 4])
+        q = torch.tensor(thr) / obj
+        if float(q) < 1:
+            gl = torch.log(q / (1 - q))
+            t[0, 1, k, 5:45] = gl
+            t[0, 1, k, 45:65] = torch.nextafter(gl, torch.tensor(10.0))
+            t[0, 1, k, 65:85] = torch.nextafter(gl, torch.tensor(-10.0))
+    dev_logits = [x.cuda().to(dtype) for x in logits]       # kept alive: lv holds raw pointers into them
+    pred, _, lv = ops.decode(dev_logits, strides, ag, na, no)
+    for kw in (dict(conf_thres=0.001, iou_thres=0.65), dict(conf_thres=0.05, iou_thres=0.5),
+               dict(conf_thres=0.25, iou_thres=0.45), dict(conf_thres=0.9, iou_thres=0.45),
+               dict(conf_thres=0.05, iou_thres=0.5, classes=[0, 3, 79])):
+        a = non_max_suppression(pred, multi_label=True, max_det=300, **kw)
+        b = _run_nms(None, B, pred.shape[1], no, kw['conf_thres'], kw['iou_thres'], kw.get('classes'), False, True, 30000,
+                     300, pred.device, levels=lv)
+        assert [x.shape[0] for x in a] == [x.shape[0] for x in b], kw
+        assert np.array_equal(_flat(a), _flat(b)), kw
+        r = non_max_suppression_ref(pred.cpu(), multi_label=True, **kw)
+        assert np.array_equal(_flat(a), _flat(r)), kw
+    assert sum(x.shape[0] for x in a) > 0

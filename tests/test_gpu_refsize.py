@@ -118,7 +118,7 @@ def test_full_size_fp32_mode_matches_reference(case, gold):
 
 # floor of the IoU>=0.5 same-class agreement of the bf16 detections with the reference's fp32 detections (conf 0.001:
 # every image saturates max_det, so rank perturbations at the cut move rows in and out); measured values: BASELINE.md
-BF16_AGREE_FLOOR = 0.60
+BF16_AGREE_FLOOR = 0.85
 
 
 @pytest.mark.parametrize('case', FULL_CASES, ids=[f'{c[0]}_{c[2]}' for c in FULL_CASES])
@@ -144,5 +144,5 @@ def test_full_size_bf16_mode_vs_reference(case, gold):
     stats.update({'detections_matched_iou50': a50, 'detections_matched_iou90': a90})
     _record(f'{name}_{H} bf16', stats)
     assert stats['box_err_over_tol_p99'] <= 1.0 and stats['score_err_p99'] <= 0.03
-    assert stats['box_err_over_tol_max'] <= 4.0 and stats['score_err_max'] <= 0.12, stats
+    assert stats["box_err_over_tol_max"] <= 1.0 and stats["score_err_max"] <= 0.03, stats      # the MAX is inside the stated tolerance too
     assert min(a50) >= BF16_AGREE_FLOOR, stats

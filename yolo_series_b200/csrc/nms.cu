@@ -502,11 +502,21 @@ template <> struct Vec4Load<__nv_bfloat16> {
   }
 };
 
-template <typename TL>
+// Multi-label mode (ML, general.py:679-681: every (row, class) with conf > conf_thres is a candidate) keeps the
+// thread-per-row walk.  A class can only be a candidate if fl(sigmoid(l_c) * obj) > conf_thres, so per row a logit gate
+// g is derived from logit(conf_thres / obj) and PROVEN safe before use: with s_hi = sigmoid_rn_(g) stepped up eight ulps
+// (sigmoid_rn_ is monotone up to a few ulps) the test fl(s_hi * obj) <= conf_thres implies that no logit below g can
+// pass; classes below the gate are dismissed four per branch without evaluating their sigmoid, the others are
+// evaluated exactly as the reference does.  If the proof fails the gate is lowered once and then dropped (full scan).
+// Rows of a warp emit different numbers of keys: the 32 lanes walk the classes in lock step and compact each class's
+// keys with a ballot into a per-warp buffer that is flushed with one global atomic per ~200 keys.
+constexpr int kMlBuf = 256;          // keys buffered per warp between flushes (a class step adds at most 4 * 32)
+
+template <typename TL, bool ML>
 __global__ void __launch_bounds__(kFbThreads) k_filter_cells(const FilterParams P) {
   extern __shared__ __align__(16) unsigned char fb_smem[];
   float* tile = reinterpret_cast<float*>(fb_smem);             // [cells_per_tile][c_stride + 1]
-  __shared__ uint64_t kbuf[kFbThreads];
+  __shared__ uint64_t kbuf[ML ? (kFbThreads / 32) * kMlBuf : kFbThreads];
   __shared__ int s_n, s_base;
   const int tid = threadIdx.x, lane = tid & 31;
   const int b = blockIdx.x / P.blocks_per_img;
@@ -554,6 +564,84 @@ __global__ void __launch_bounds__(kFbThreads) k_filter_cells(const FilterParams 
       }
     }
     __syncthreads();
+    if (ML) {
+      uint64_t* wbuf = kbuf + (tid >> 5) * kMlBuf;
+      int n_w = 0;                                             // warp-uniform
+      auto flush = [&]() {
+        __syncwarp();
+        int base = 0;
+        if (lane == 0 && n_w) base = atomicAdd(P.count + b, n_w);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        for (int i = lane; i < n_w; i += 32) {
+          const int slot = base + i;
+          if (slot < P.cap) P.keys[(size_t)b * P.cap + slot] = wbuf[i];
+          else if (P.overflow) *P.overflow = 1;
+        }
+        __syncwarp();
+        n_w = 0;
+      };
+      const bool live = a < P.na && cl < nc_tile;
+      const float* r = tile + (live ? cl * pitch + a * P.no : 0);
+      const int cell = c0 + cl;
+      const int row = L.row_off + a * ncells + cell;
+      float obj = 0.f, gate = INFINITY;
+      if (live) {
+        obj = sigmoid_rn_(r[4]);
+        if (obj > P.conf_thres) {                              // general.py:637,653
+          const float q = __fdividef(P.conf_thres, obj);       // in (0, 1); only a starting point, the proof is below
+          float g = fminf(__logf(__fdividef(q, 1.0f - q)), 30.0f) - 0.01f;
+          gate = -INFINITY;
+#pragma unroll
+          for (int attempt = 0; attempt < 2; ++attempt) {
+            const float s_hi = __uint_as_float(__float_as_uint(sigmoid_rn_(g)) + 8u);
+            if (__fmul_rn(s_hi, obj) <= P.conf_thres) { gate = g; break; }
+            g -= 0.25f;
+          }
+          if (!(P.conf_thres >= 0.f)) gate = -INFINITY;        // negative / NaN thresholds: no shortcut
+        }
+      }
+      bool any_emit = false;
+      for (int c = 0; c < P.nc; c += 4) {
+        float v[4];
+        bool pass = false;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          v[u] = (live && c + u < P.nc) ? r[5 + c + u] : -INFINITY;
+          pass |= !(v[u] < gate);
+        }
+        if (!__any_sync(0xffffffffu, pass)) continue;
+        if (n_w + 128 > kMlBuf) flush();
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          bool e = false;
+          float conf = 0.f;
+          if (!(v[u] < gate)) {
+            conf = __fmul_rn(sigmoid_rn_(v[u]), obj);          // general.py:673
+            e = conf > P.conf_thres && class_allowed(P, c + u);  // general.py:680, 687-688
+          }
+          const unsigned m = __ballot_sync(0xffffffffu, e);
+          if (e) {
+            const uint32_t idx = (uint32_t)row * (uint32_t)P.nc + (uint32_t)(c + u);
+            wbuf[n_w + __popc(m & ((1u << lane) - 1u))] = ((uint64_t)(~__float_as_uint(conf)) << 32) | idx;
+            any_emit = true;
+          }
+          n_w += __popc(m);
+        }
+      }
+      flush();
+      if (any_emit) {
+        const int gy = L.magic_nx ? (int)__umulhi((unsigned)cell, L.magic_nx) : cell;
+        const int gx = cell - gy * L.nx;
+        const float sx = sigmoid_rn_(r[0]), sy = sigmoid_rn_(r[1]), sw = sigmoid_rn_(r[2]), sh = sigmoid_rn_(r[3]);
+        const float bx = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(sx, 2.f), 0.5f), (float)gx), L.stride);
+        const float by = __fmul_rn(__fadd_rn(__fsub_rn(__fmul_rn(sy, 2.f), 0.5f), (float)gy), L.stride);
+        const float w2 = __fmul_rn(sw, 2.f), h2 = __fmul_rn(sh, 2.f);
+        *reinterpret_cast<float4*>(P.boxes + ((size_t)b * P.A + row) * 4) =
+            make_float4(bx, by, __fmul_rn(__fmul_rn(w2, w2), L.anchor_wh[2 * a]), __fmul_rn(__fmul_rn(h2, h2), L.anchor_wh[2 * a + 1]));
+      }
+      __syncthreads();                                         // the tile is re-staged next
+      continue;
+    }
     bool emit = false;
     unsigned long long key = 0ull;
     if (a < P.na && cl < nc_tile) {
@@ -1218,7 +1306,7 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
     F.blocks_per_img = (A + F.rows_per_block - 1) / F.rows_per_block;
     const int grid = B * F.blocks_per_img;
     const size_t fb_smem = (size_t)kFbThreads * (F.no | 1) * 4;
-    bool cells_ok = fused && !F.multi_label && F.na >= 1 && F.na <= 8;
+    bool cells_ok = fused && F.na >= 1 && F.na <= 8;
     int max_cs = 0;
     for (int l = 0; cells_ok && l < F.nl; ++l) {
       const HeadLevelDev& L = F.lv[l];
@@ -1244,13 +1332,14 @@ static int nms_common(FilterParams& F, bool fused, int logits_dtype, double iou_
       }
       F.blocks_per_img = off;
       const int grid3 = B * off;
-      if (logits_dtype == YB_F32) {
-        YB_CUDA(cudaFuncSetAttribute(k_filter_cells<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cells_smem));
-        k_filter_cells<float><<<grid3, kFbThreads, cells_smem, s>>>(F);
-      } else {
-        YB_CUDA(cudaFuncSetAttribute(k_filter_cells<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cells_smem));
-        k_filter_cells<__nv_bfloat16><<<grid3, kFbThreads, cells_smem, s>>>(F);
-      }
+#define YB_CELLS_LAUNCH(T, ML)                                                                                            \
+      do {                                                                                                               \
+        YB_CUDA(cudaFuncSetAttribute(k_filter_cells<T, ML>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cells_smem)); \
+        k_filter_cells<T, ML><<<grid3, kFbThreads, cells_smem, s>>>(F);                                                  \
+      } while (0)
+      if (logits_dtype == YB_F32) { if (F.multi_label) YB_CELLS_LAUNCH(float, true); else YB_CELLS_LAUNCH(float, false); }
+      else { if (F.multi_label) YB_CELLS_LAUNCH(__nv_bfloat16, true); else YB_CELLS_LAUNCH(__nv_bfloat16, false); }
+#undef YB_CELLS_LAUNCH
     } else if (!fused && !F.multi_label && F.nc > 1 && (F.no & 1) && ((long long)A * F.no) % 4 == 0 &&
                (uintptr_t)F.pred % 16 == 0 && (size_t)kBkRows * F.no * 4 * 2 <= 200 * 1024 &&
                getenv("YB_NMS_NO_BULK") == nullptr) {
