@@ -151,6 +151,19 @@ int yb_nms(const float* pred, int B, int A, int no, float conf_thres, double iou
            int cand_cap, void* workspace, size_t workspace_bytes, float* out, int* counts,
            int* overflow, void* stream);
 
+/* yb_nms with NO allocation and NO caller workspace.  This entry point has no counterpart in the reference; it was
+ * added for callers that cannot call cudaMalloc (CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  The scratch yb_nms takes from the caller lives in a file-scope static
+ * __device__ array of yb_nms_static_capacity() = 16 MiB (held by every GPU that loads the library until exit), e.g.
+ * 32 images x 25 200 rows in best-class mode.  Larger problems (B*(18*A + 4) + ~1 KiB bytes in best-class mode,
+ * B*(16*A*nc + 2*A + 4) with multi_label) are rejected with YB_ERR_WORKSPACE before anything is launched.  Same
+ * results as yb_nms.  All calls share the array: calls that overlap on the GPU (different streams / threads) race;
+ * serialise them on one stream.  The function itself calls no cudaMalloc / cudaFree or allocating routine. */
+size_t yb_nms_static_capacity(void);
+int yb_nms_static(const float* pred, int B, int A, int no, float conf_thres, double iou_thres,
+                  const int* classes, int n_classes, int agnostic, int multi_label, int max_nms, int max_det,
+                  float* out, int* counts, int* overflow /* device, nullable */, void* stream);
+
 /* Fused decode -> candidate filter -> NMS: same result as yb_decode followed by yb_nms, without
  * materialising pred in HBM (the north-star's "one fused decode kernel ... threshold compaction"). */
 int yb_decode_nms(const yb_head_level* levels, int nl, int na, int no, float conf_thres,

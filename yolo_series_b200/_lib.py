@@ -19,7 +19,7 @@ EXPORTS = [
     'yb_last_error', 'yb_abi_version', 'yb_conv2d', 'yb_conv_plan_create', 'yb_conv_plan_launch',
     'yb_conv_plan_destroy', 'yb_maxpool2x2', 'yb_maxpool_s1', 'yb_spp3',
     'yb_upsample2x', 'yb_copy', 'yb_add', 'yb_stage_input', 'yb_stem_conv', 'yb_decode', 'yb_nms_workspace_bytes',
-    'yb_nms', 'yb_decode_nms', 'yb_engine_create', 'yb_engine_forward', 'yb_engine_num_launches', 'yb_engine_profile',
+    'yb_nms', 'yb_nms_static', 'yb_nms_static_capacity', 'yb_decode_nms', 'yb_engine_create', 'yb_engine_forward', 'yb_engine_num_launches', 'yb_engine_profile',
     'yb_engine_op_kernel', 'yb_engine_destroy', 'yb_letterbox', 'yb_scale_coords', 'yb_scale_img', 'yb_decode_tta', 'yb_box_iou',
     'yb_match_detections', 'yb_decode_nms_gather', 'yb_peer_wait', 'yb_peer_alloc', 'yb_peer_open', 'yb_peer_close',
     'yb_peer_free',
@@ -111,6 +111,10 @@ def lib():
     L.yb_nms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_double, C.POINTER(C.c_int), C.c_int,
                          C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p,
                          C.c_void_p, C.c_void_p, C.c_void_p]
+    L.yb_nms_static_capacity.restype = C.c_size_t
+    L.yb_nms_static_capacity.argtypes = []
+    L.yb_nms_static.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_double, C.POINTER(C.c_int), C.c_int,
+                                C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.yb_decode_nms.argtypes = [C.POINTER(HeadLevel), C.c_int, C.c_int, C.c_int, C.c_float, C.c_double,
                                 C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                 C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]

@@ -1457,6 +1457,59 @@ extern "C" int yb_nms(const float* pred, int B, int A, int no, float conf_thres,
                     workspace_bytes, out, counts, overflow, (cudaStream_t)stream);
 }
 
+// ---- yb_nms_static: yb_nms with its workspace in library-owned static device memory (no allocation anywhere).
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The array is part of the module
+// image: every GPU that loads the library holds kStaticWsBytes until exit.  All calls share it and it keeps the last
+// call's contents -- nms_common clears the per-image candidate counters (the only part that must start at zero) on
+// every call; calls that overlap on the GPU (two streams, two host threads) race on it.
+constexpr size_t kStaticWsBytes = (size_t)16 << 20;      // 16 MiB: e.g. 32 images x 25 200 rows in best-class mode
+static __device__ __align__(256) unsigned char g_static_ws[kStaticWsBytes];
+
+// In host code `g_static_ws` is only a host-side stand-in for the symbol, NOT a device address: the device address is
+// looked up once per device (with that device current) and cached.
+static int static_ws_ptr(void** out) {
+  constexpr int kMaxDev = 64;
+  static void* cache[kMaxDev] = {nullptr};
+  int dev = 0;
+  YB_CUDA(cudaGetDevice(&dev));
+  YB_CHECK_ARG(dev >= 0 && dev < kMaxDev, "yb_nms_static: device ordinal %d out of range", dev);
+  if (!cache[dev]) {
+    void* p = nullptr;
+    YB_CUDA(cudaGetSymbolAddress(&p, g_static_ws));
+    YB_CHECK_ARG(p != nullptr && (uintptr_t)p % 256 == 0, "yb_nms_static: bad symbol address");
+    cache[dev] = p;
+  }
+  *out = cache[dev];
+  return YB_OK;
+}
+
+extern "C" size_t yb_nms_static_capacity(void) { return kStaticWsBytes; }
+
+extern "C" int yb_nms_static(const float* pred, int B, int A, int no, float conf_thres, double iou_thres,
+                             const int* classes, int n_classes, int agnostic, int multi_label, int max_nms, int max_det,
+                             float* out, int* counts, int* overflow, void* stream) {
+  YB_CHECK_ARG(pred, "yb_nms_static: null pred");
+  YB_CHECK_ARG(B > 0 && A > 0 && no > 5, "yb_nms_static: need B, A > 0 and no >= 6");
+  FilterParams F;
+  memset(&F, 0, sizeof(F));
+  F.pred = pred; F.B = B; F.A = A; F.no = no; F.nc = no - 5; F.conf_thres = conf_thres;
+  F.multi_label = (multi_label && F.nc > 1) ? 1 : 0;  // general.py:645
+  F.cap = resolve_cap(A, F.nc, F.multi_label, 0);
+  // size check in 64-bit host arithmetic BEFORE anything is launched
+  const double need_est = (double)B * 4 + 2.0 * (double)B * (double)F.cap * 8 + (double)B * (double)A * 2 + 4 * 256;
+  if (need_est > (double)kStaticWsBytes || carve(nullptr, B, A, F.cap, false).total > kStaticWsBytes) {
+    set_error("yb_nms_static: B=%d A=%d no=%d multi_label=%d needs %.0f bytes of scratch, the static array holds %zu "
+              "(use yb_nms with a caller workspace)", B, A, no, F.multi_label, need_est, kStaticWsBytes);
+    return YB_ERR_WORKSPACE;
+  }
+  void* ws = nullptr;
+  const int rc = static_ws_ptr(&ws);
+  if (rc) return rc;
+  return nms_common(F, false, YB_F32, iou_thres, agnostic, max_nms, max_det, classes, n_classes, ws, kStaticWsBytes, out,
+                    counts, overflow, (cudaStream_t)stream);
+}
+
 extern "C" int yb_decode_nms_gather(const yb_head_level* levels, int nl, int na, int no, float conf_thres,
                                     double iou_thres, const int* classes, int n_classes, int agnostic, int multi_label,
                                     int max_nms, int max_det, int cand_cap, void* workspace, size_t workspace_bytes,
