@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define YB_ABI_VERSION 2
+#define YB_ABI_VERSION 3
 
 typedef enum {
   YB_OK = 0,
@@ -77,6 +77,9 @@ typedef struct {
   yb_tensor res;
   /* tuning overrides, 0 = auto */
   int32_t tile_n, stages;
+  /* CTA pairs (clusters of two CTAs, tcgen05 cta_group::2: one M = 256 MMA per pair, each CTA loads half of the
+   * weight tile): 0 = cost model decides, 1 = force, -1 = never */
+  int32_t pair;
 } yb_conv_desc;
 
 int yb_conv2d(const yb_conv_desc* d, void* stream);
@@ -227,6 +230,7 @@ typedef struct {
   int32_t weight;         /* index into weights/biases (-1 = none) */
   int32_t cin_pad, cout_pad;
   int32_t tile_n, stages; /* 0 = auto */
+  int32_t pair;           /* yb_conv_desc.pair */
 } yb_op;
 
 typedef struct yb_engine yb_engine;

@@ -167,3 +167,42 @@ def test_conv_tc_generic_kernel_on_3x3(case):
     ref = _ref_conv(x, w, b, s, act, 0.1, ups)
     y = ops.conv2d(_nhwc(x).cuda().bfloat16(), w, b, s, act, 0.1, ups, tile_n=-1)
     assert torch.allclose(_nchw(y[..., :Co].float().cpu()), ref, rtol=1.2e-2, atol=1.2e-2)
+
+
+PAIR_CASES = [
+    # (N, H, W, Cin, Cout, k, s, act, tile_n)   tile_n < 0 forces the generic kernel (-1: its own choice of N tile)
+    (2, 20, 20, 64, 64, 1, 1, 1, -1),          # 7 M tiles: the last pair has a tile past the end
+    (1, 20, 20, 512, 255, 1, 1, 0, -1),        # head-like: Cout 255, 8 K chunks
+    (4, 80, 80, 256, 256, 1, 1, 1, -256),      # 200 M tiles on 74 pairs: several rounds, ring and TMEM phases wrap
+    (4, 80, 80, 256, 256, 1, 1, 1, -128),      # two N tiles
+    (2, 20, 20, 1024, 512, 1, 1, 1, -1),       # long K
+    (2, 40, 40, 128, 64, 1, 1, 2, -64),        # N tile 64 -> 32 weight rows per CTA, LeakyReLU
+    (2, 24, 40, 64, 128, 3, 2, 1, -1),         # stride-2 3x3 (element strides, zero-filled borders)
+    (2, 20, 20, 128, 256, 3, 1, 1, -1),        # 3x3 stride 1 through the per-tap kernel
+    (3, 12, 20, 96, 96, 3, 1, 1, -1),          # ragged spatial tiles, Cin not a multiple of 64
+    (1, 8, 8, 64, 32, 1, 1, 1, -1),            # a single M tile: one CTA of the pair works on zeros
+]
+
+
+@pytest.mark.parametrize('case', PAIR_CASES, ids=[str(c) for c in PAIR_CASES])
+def test_conv_tc_cta_pairs(case):
+    """pair=1 runs the generic kernel as clusters of two CTAs (tcgen05.mma.cta_group::2, M = 256, each CTA loads half
+    of the weight tile).  Same K order per output element as the single-CTA kernel -> bit-identical to it, and within
+    the bf16 tolerance of the fp32 PyTorch reference."""
+    from yolo_series_b200 import ops
+    N, H, W, Ci, Co, k, s, act, tn = case
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn((N, Ci, H, W), generator=g).bfloat16().float()
+    w = (torch.randn((Co, Ci, k, k), generator=g) / (Ci * k * k) ** 0.5).bfloat16().float()
+    b = torch.randn((Co,), generator=g)
+    ref = _ref_conv(x, w, b, s, act, 0.1, 1)
+    xd = _nhwc(x).cuda().bfloat16()
+    y1 = ops.conv2d(xd, w, b, s, act, 0.1, 1, tile_n=tn, pair=-1)
+    y2 = ops.conv2d(xd, w, b, s, act, 0.1, 1, tile_n=tn, pair=1)
+    torch.cuda.synchronize()
+    got = _nchw(y2[..., :Co].float().cpu())
+    assert torch.allclose(got, ref, rtol=1.2e-2, atol=1.2e-2), float((got - ref).abs().max())
+    assert torch.equal(y1, y2)
+    # fp32 output (head logits) through the pair path
+    y3 = ops.conv2d(xd, w, b, s, act, 0.1, 1, tile_n=tn if tn > -256 else -128, pair=1, out_dtype=torch.float32)
+    assert torch.allclose(_nchw(y3[..., :Co].cpu()), ref, rtol=1.2e-2, atol=1.2e-2)

@@ -88,6 +88,25 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), int grid, int block, siz
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// Same, as clusters of two CTAs (CTA pairs for tcgen05 cta_group::2); `grid` must be even.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl_pairs(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid, 1, 1);
+  cfg.blockDim = dim3((unsigned)block, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  static const bool off = getenv("YB_NO_PDL") != nullptr;
+  cfg.attrs = at;
+  cfg.numAttrs = off ? 1 : 2;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // internal launchers shared by the C ABI wrappers and the engine
 int conv_fp32_launch(const yb_conv_desc& d, cudaStream_t s);
 

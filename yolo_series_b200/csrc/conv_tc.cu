@@ -38,7 +38,8 @@ struct ConvTcArgs {
   int sw_mode;                     // UMMA layout type: 2 = SW128, 4 = SW64, 6 = SW32
   int tmem_cols;
   int bias_len;
-  int total_tiles;
+  int total_tiles;                 // work units: (m, n) tiles, or (pair of m tiles, n) in pair mode
+  int pair;                        // 1: CTA pairs (clusters of 2, tcgen05 cta_group::2, M = 256 per MMA)
   uint32_t idesc;
 };
 
@@ -46,14 +47,23 @@ struct ConvTcArgs {
 // ahead across tile boundaries (smem ring of `stages` K-chunks), accumulators are double-buffered in
 // TMEM so the MMA of tile i+1 overlaps the epilogue of tile i, and the epilogue owns a dedicated
 // swizzled staging buffer for the TMA store.
+//
+// PAIR = true (launched as clusters of two CTAs): the two CTAs of a pair take two consecutive M tiles of the same N
+// tile and run them as ONE M = 256 tcgen05.mma.cta_group::2 -- each CTA loads its own A tile and only HALF of the
+// weight tile (rows n0 + rank * BN/2 ...), so the weight bytes through L2 -> SM and through shared memory are halved
+// (tc_common.cuh "CTA pairs").  Everything below is per CTA unless it says "leader".
+template <bool PAIR>
 __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant__ ConvTcArgs G) {
   extern __shared__ unsigned char smem_dyn[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0u;
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
   unsigned char* tiles_ptr = smem_dyn + (tiles - raw);
   const uint32_t a_bytes = 128u * G.BK * 2u;
-  const uint32_t b_bytes = (uint32_t)G.BN * G.BK * 2u;
+  const uint32_t bn_cta = PAIR ? (uint32_t)G.BN / 2u : (uint32_t)G.BN;      // weight rows this CTA holds
+  const uint32_t b_bytes = bn_cta * G.BK * 2u;
   // resident mode: [all taps x chunks weight tiles][A ring]; streaming mode: ring of (A, B) stages
   const uint32_t res_bytes = G.resident ? b_bytes * (uint32_t)(G.taps * G.kchunks) : 0u;
   const uint32_t stage_bytes = G.resident ? a_bytes : a_bytes + b_bytes;
@@ -75,35 +85,51 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     tma_prefetch_desc(&G.tm_b);
     for (int i = 0; i < G.n_store_maps; ++i) tma_prefetch_desc(&G.tm_y[i]);
     for (int s = 0; s < G.stages; ++s) { mbar_init(bar_full0 + 8u * s, 1); mbar_init(bar_empty0 + 8u * s, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull0 + 8u * i, 1); mbar_init(bar_tempty0 + 8u * i, 1); }
+    // tmem_empty: one arrival per CTA of the pair (the leader's MMA warp waits for both epilogues)
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull0 + 8u * i, 1); mbar_init(bar_tempty0 + 8u * i, PAIR ? 2 : 1); }
     mbar_init(bar_res, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"((uint32_t)G.tmem_cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (PAIR) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"((uint32_t)G.tmem_cols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"((uint32_t)G.tmem_cols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   for (int i = threadIdx.x; i < kMaxBias; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
+  if (PAIR) cluster_sync_all();     // the peer's barriers must exist before anything signals them
+  else __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
   const int total_chunks = G.taps * G.kchunks;
   const int tiles_m_per_img = G.tiles_w * G.tiles_h;
   // Tile walk.  Streaming: t = blockIdx.x + i * grid over (m, n) pairs, n fastest.  Resident: the CTA keeps one
   // N tile (blockIdx.x % tiles_n) and strides over the M tiles.
-  const int res_n = blockIdx.x % G.tiles_n;
-  const int t_first = G.resident ? blockIdx.x / G.tiles_n : blockIdx.x;
-  const int t_step = G.resident ? gridDim.x / G.tiles_n : gridDim.x;
+  // In pair mode the work unit is (pair of M tiles, N tile) and the walker is the pair: unit u covers M tiles
+  // 2u and 2u + 1 (this CTA: 2u + rank; a tile past the end loads zeros and stores nothing -- TMA clips both).
+  const int walker = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int walkers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int res_n = walker % G.tiles_n;
+  const int t_first = G.resident ? walker / G.tiles_n : walker;
+  const int t_step = G.resident ? walkers / G.tiles_n : walkers;
   const int t_end = G.resident ? G.total_tiles / G.tiles_n : G.total_tiles;
+  const int b_row0 = (int)(rank * bn_cta);            // first weight row of this CTA inside the N tile
   if (G.resident && warp == 0) {
     // weights are constants: fetch them while the previous kernel is still draining
     if (elect_one()) {
-      mbar_expect_tx(bar_res, res_bytes);
+      if (leader) mbar_expect_tx(bar_res, PAIR ? 2u * res_bytes : res_bytes);
       for (int tap = 0; tap < G.taps; ++tap)
-        for (int kk = 0; kk < G.kchunks; ++kk)
-          tma_load_3d(&G.tm_b, bar_res, tiles + (uint32_t)(tap * G.kchunks + kk) * b_bytes, kk * G.BK, tap, res_n * G.BN);
+        for (int kk = 0; kk < G.kchunks; ++kk) {
+          const uint32_t dst = tiles + (uint32_t)(tap * G.kchunks + kk) * b_bytes;
+          if (PAIR) tma_load_3d_2sm(&G.tm_b, bar_res, dst, kk * G.BK, tap, res_n * G.BN + b_row0);
+          else tma_load_3d(&G.tm_b, bar_res, dst, kk * G.BK, tap, res_n * G.BN);
+        }
     }
     __syncwarp();
   }
@@ -113,11 +139,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   if (warp == 0) {
     // ================================ TMA producer ================================
     // Warp-uniform control flow, one elected lane issues the copies (coordinates live in uniform registers).
-    const uint32_t tx = (uint32_t)(G.BW * G.BH) * G.BK * 2u + (G.resident ? 0u : b_bytes);
+    const uint32_t tx1 = (uint32_t)(G.BW * G.BH) * G.BK * 2u + (G.resident ? 0u : b_bytes);
+    const uint32_t tx = PAIR ? 2u * tx1 : tx1;      // the leader's barrier collects the bytes of both CTAs
     uint32_t s = 0, ph = 1;  // ring slot + parity to wait for on its empty barrier
     for (int t = t_first; t < t_end; t += t_step) {
       const int n_tile = G.resident ? res_n : t % G.tiles_n;
       int m_tile = G.resident ? t : t / G.tiles_n;
+      if (PAIR) m_tile = 2 * m_tile + (int)rank;
       const int img = m_tile / tiles_m_per_img;
       m_tile -= img * tiles_m_per_img;
       const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
@@ -130,10 +158,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
           mbar_wait(bar_empty0 + 8u * s, ph);
           if (elect_one()) {
             const uint32_t full = bar_full0 + 8u * s;
-            mbar_expect_tx(full, tx);
+            if (leader) mbar_expect_tx(full, tx);
             const uint32_t sa = ring + s * stage_bytes;
-            tma_load_4d(&G.tm_a, full, sa, kk * G.BK, cw, chh, img);
-            if (!G.resident) tma_load_3d(&G.tm_b, full, sa + a_bytes, kk * G.BK, tap, n0);
+            if (PAIR) {
+              tma_load_4d_2sm(&G.tm_a, full, sa, kk * G.BK, cw, chh, img);
+              if (!G.resident) tma_load_3d_2sm(&G.tm_b, full, sa + a_bytes, kk * G.BK, tap, n0 + b_row0);
+            } else {
+              tma_load_4d(&G.tm_a, full, sa, kk * G.BK, cw, chh, img);
+              if (!G.resident) tma_load_3d(&G.tm_b, full, sa + a_bytes, kk * G.BK, tap, n0);
+            }
           }
           __syncwarp();
           if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
@@ -142,8 +175,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
       }
     }
   } else if (warp == 1) {
-    // ================================ MMA issuer ==================================
+    // ================================ MMA issuer (pair mode: the leader CTA only) ==================================
     // Whole warp runs the (uniform) control flow; one elected lane issues tcgen05.mma / commit.
+    if (leader) {
     const uint32_t sbo = 8u * (uint32_t)G.BK * 2u;
     const int nk = G.BK / 16;
     const uint32_t hi32 = (uint32_t)(make_smem_desc(0, sbo, (uint32_t)G.sw_mode) >> 32);
@@ -154,7 +188,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     int it = 0;
     for (int t = t_first; t < t_end; t += t_step, ++it) {
       const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
-      mbar_wait(bar_tempty0 + 8u * acc, aph ^ 1u);       // epilogue has drained this accumulator
+      if (PAIR) mbar_wait_cluster(bar_tempty0 + 8u * acc, aph ^ 1u);   // both CTAs' epilogues have drained it
+      else mbar_wait(bar_tempty0 + 8u * acc, aph ^ 1u);  // epilogue has drained this accumulator
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t tmem_d = tmem_base + acc * (uint32_t)G.BN;
       for (int c = 0; c < total_chunks; ++c) {
@@ -164,6 +199,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
         const uint32_t db = G.resident ? bres + (uint32_t)c * bstep : da + boff;
         if (elect_one()) {
           const uint32_t acc0 = (uint32_t)(c != 0);
+          if (PAIR) {
+            if (nk == 4) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) umma_bf16_lh_2sm(tmem_d, da + 2u * k, db + 2u * k, hi32, G.idesc, k ? 1u : acc0);
+            } else if (nk == 2) {
+#pragma unroll
+              for (int k = 0; k < 2; ++k) umma_bf16_lh_2sm(tmem_d, da + 2u * k, db + 2u * k, hi32, G.idesc, k ? 1u : acc0);
+            } else {
+              umma_bf16_lh_2sm(tmem_d, da, db, hi32, G.idesc, acc0);
+            }
+            umma_commit_2sm(bar_empty0 + 8u * s);   // frees this stage in BOTH CTAs once these MMAs retire
+          } else {
           if (nk == 4) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) umma_bf16_lh(tmem_d, da + 2u * k, db + 2u * k, hi32, G.idesc, k ? 1u : acc0);
@@ -174,12 +221,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
             umma_bf16_lh(tmem_d, da, db, hi32, G.idesc, acc0);
           }
           umma_commit(bar_empty0 + 8u * s);   // frees the smem stage once these MMAs retire
+          }
         }
         __syncwarp();
         if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
       }
-      if (elect_one()) umma_commit(bar_tfull0 + 8u * acc);
+      if (elect_one()) { if (PAIR) umma_commit_2sm(bar_tfull0 + 8u * acc); else umma_commit(bar_tfull0 + 8u * acc); }
       __syncwarp();
+    }
     }
   } else {
     // ================================ epilogue ====================================
@@ -210,6 +259,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
         const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
         const int n_tile = G.resident ? res_n : t % G.tiles_n;
         int m_tile = G.resident ? t : t / G.tiles_n;
+        if (PAIR) m_tile = 2 * m_tile + (int)rank;
         const int img = m_tile / tiles_m_per_img;
         m_tile -= img * tiles_m_per_img;
         const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
@@ -232,7 +282,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to TMA
         asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(nthr) : "memory");
         if (store_thread) {
-          mbar_arrive(bar_tempty0 + 8u * acc);   // every warp of the tile has read this accumulator
+          // every warp of the tile has read this accumulator: hand it back to the (leader's) MMA warp
+          if (PAIR && !leader) mbar_arrive_remote(bar_tempty0 + 8u * acc, 0u);
+          else mbar_arrive(bar_tempty0 + 8u * acc);
           const int per_group = G.out_f32 ? 32 : 64;
           const int ngroups = (G.BN + per_group - 1) / per_group;
           for (int mp = 0; mp < G.n_store_maps; ++mp)
@@ -246,6 +298,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     else if (G.act == YB_ACT_LEAKY) run(std::integral_constant<int, YB_ACT_LEAKY>{});
     else run(std::integral_constant<int, YB_ACT_NONE>{});
     if ((ew & 3) == 0 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  if (PAIR) {
+    // neither CTA may leave (or free TMEM) while the other can still signal its barriers or read its operands
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    cluster_sync_all();
+    if (warp == 1) {
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G.tmem_cols)
+                   : "memory");
+    }
+    return;
   }
   __syncthreads();
   if (warp == 1) {
@@ -268,49 +331,64 @@ constexpr size_t kAuxBytes = 8 * (2 * 12 + 6) + 16 + (size_t)kMaxBias * 4 + 64;
 // one round per tile: each epilogue warp converts half of the tile's 32-column chunks
 static int epi_cpr_for(int bn, int y_es) { (void)y_es; return (bn / 32 + 1) / 2; }
 
-static size_t tile_smem(int bn, int bk, int y_es, bool resident, int chunks, int stages, int ring = 1) {
-  const size_t a = (size_t)128 * bk * 2, b = (size_t)bn * bk * 2;
+// `bn_cta` = weight rows a CTA holds (BN, or BN / 2 in pair mode); the output staging is always the CTA's own 128 x BN.
+static size_t tile_smem(int bn, int bk, int y_es, bool resident, int chunks, int stages, int ring = 1, int bn_cta = 0) {
+  if (!bn_cta) bn_cta = bn;
+  const size_t a = (size_t)128 * bk * 2, b = (size_t)bn_cta * bk * 2;
   const size_t out = (size_t)ring * (y_es == 4 ? 32768 : 16384) * epi_cpr_for(bn, y_es);
   return 1024 + (resident ? b * chunks + a * stages : (a + b) * stages) + out + kAuxBytes;
 }
 
-// Tile-N / weight-residency heuristic: estimated cycles = rounds of the persistent grid x per-tile cost, where a
-// tile costs max(MMA issue, operand bytes / ~42 B/clk/SM of L2->smem throughput, epilogue).  With resident
-// weights the per-tile operand bytes are the activations only and the weights are fetched once per CTA.
-static void pick_tile(int cout, long long m_tiles, int chunks, int bk, int y_es, int* bn_out, int* resident_out) {
+// Tile-N / weight-residency / CTA-pair heuristic: estimated cycles = rounds of the persistent grid x per-tile cost,
+// where a tile costs max(MMA issue, operand bytes / ~42 B/clk/SM of L2->smem throughput, epilogue).  With resident
+// weights the per-tile operand bytes are the activations only and the weights are fetched once per CTA.  In pair mode
+// (cta_group::2) every CTA loads half of the weight tile: same MMA time per tile, fewer operand bytes, but the walkers
+// are pairs (half as many) each covering two M tiles, and a pair waits for the slower of its two CTAs.
+// pair_mode: 0 = choose, 1 = force, -1 = never.
+static void pick_tile(int cout, long long m_tiles, int chunks, int bk, int y_es, int pair_mode, int* bn_out, int* resident_out,
+                      int* pair_out) {
   const int cands[4] = {32, 64, 128, 256};
   static const char* force_env = getenv("YB_RESIDENT");   // tuning aid: 0 = never, 1 = whenever it fits
   const int force = force_env ? atoi(force_env) : -1;
-  int best = 64, best_res = 0;
+  static const char* pair_env = getenv("YB_PAIR");        // tuning aid: overrides a pair_mode of 0
+  if (pair_mode == 0 && pair_env) pair_mode = atoi(pair_env);
+  int best = 64, best_res = 0, best_pair = 0;
   double best_cost = 1e30;
-  for (int i = 0; i < 4; ++i) {
-    const int bn = cands[i];
-    if (bn == 32 && cout > 32) continue;
-    if (bn > 32 && cout <= 32) continue;
-    if (y_es == 4 && bn > 128) continue;  // fp32 staging tile would not leave room for the pipeline
-    const int tiles_n = (cout + bn - 1) / bn;
-    for (int res = 0; res < 2; ++res) {
-      if (force == 0 && res) continue;
-      if (res && tiles_n != 1) continue;   // measured: splitting Cout to make the weights fit re-reads A and loses
-      if (res && (tile_smem(bn, bk, y_es, true, chunks, 4) > 227 * 1024 || tiles_n > num_sms())) continue;
-      if (!res && tile_smem(bn, bk, y_es, false, chunks, 2) > 227 * 1024) continue;
-      const long long tiles = m_tiles * tiles_n;
-      int grid = (int)(tiles < num_sms() ? tiles : num_sms());
-      if (res) grid = grid / tiles_n * tiles_n;
-      if (grid < 1) continue;
-      const double rounds = (double)((tiles + grid - 1) / grid);
-      const double mma = chunks * (bk / 16) * (bn / 2.0);
-      const double a_b = 128.0 * bk * 2, b_b = (double)bn * bk * 2;
-      const double load = chunks * (a_b + (res ? 0.0 : b_b)) / 42.0;
-      const double epi = bn * 10.0 + 600.0;
-      double tile = mma > load ? mma : load;
-      if (epi > tile) tile = epi;
-      const double cost = rounds * (tile + 400.0) + (res ? chunks * b_b / 42.0 : 0.0);
-      if (force == 1 && res) { const double c1 = cost * 1e-6; if (c1 < best_cost) { best_cost = c1; best = bn; best_res = 1; } continue; }
-      if (cost < best_cost * 0.999) { best_cost = cost; best = bn; best_res = res; }
+  for (int pr = 0; pr < 2; ++pr) {
+    if ((pr && pair_mode < 0) || (!pr && pair_mode > 0)) continue;
+    for (int i = 0; i < 4; ++i) {
+      const int bn = cands[i];
+      if (bn == 32 && cout > 32) continue;
+      if (bn > 32 && cout <= 32) continue;
+      if (y_es == 4 && bn > 128) continue;  // fp32 staging tile would not leave room for the pipeline
+      const int bn_cta = pr ? bn / 2 : bn;
+      const int tiles_n = (cout + bn - 1) / bn;
+      const int walkers_max = pr ? num_sms() / 2 : num_sms();
+      const long long units_m = pr ? (m_tiles + 1) / 2 : m_tiles;
+      for (int res = 0; res < 2; ++res) {
+        if (force == 0 && res) continue;
+        if (res && tiles_n != 1) continue;   // measured: splitting Cout to make the weights fit re-reads A and loses
+        if (res && (tile_smem(bn, bk, y_es, true, chunks, 4, 1, bn_cta) > 227 * 1024 || tiles_n > walkers_max)) continue;
+        if (!res && tile_smem(bn, bk, y_es, false, chunks, 2, 1, bn_cta) > 227 * 1024) continue;
+        const long long units = units_m * tiles_n;
+        int walkers = (int)(units < walkers_max ? units : walkers_max);
+        if (res) walkers = walkers / tiles_n * tiles_n;
+        if (walkers < 1) continue;
+        const double rounds = (double)((units + walkers - 1) / walkers);
+        const double mma = chunks * (bk / 16) * (bn / 2.0);
+        const double a_b = 128.0 * bk * 2, b_b = (double)bn_cta * bk * 2;
+        const double load = chunks * (a_b + (res ? 0.0 : b_b)) / 42.0;
+        const double epi = bn * 10.0 + 600.0;
+        double tile = mma > load ? mma : load;
+        if (epi > tile) tile = epi;
+        // pairs: cluster launch / cross-CTA handshakes cost a little per tile and at start-up
+        const double cost = rounds * (tile + (pr ? 500.0 : 400.0)) + (res ? chunks * b_b / 42.0 : 0.0) + (pr ? 1500.0 : 0.0);
+        if (force == 1 && res) { const double c1 = cost * 1e-6; if (c1 < best_cost) { best_cost = c1; best = bn; best_res = 1; best_pair = pr; } continue; }
+        if (cost < best_cost * 0.999) { best_cost = cost; best = bn; best_res = res; best_pair = pr; }
+      }
     }
   }
-  *bn_out = best; *resident_out = best_res;
+  *bn_out = best; *resident_out = best_res; *pair_out = best_pair;
 }
 
 // [Cout_pad][9][cin_pad] (Cin = 32) -> [Cout_pad][3 dy][2 pair taps][64]: a stride-2 3x3 conv over 32-channel pixels
@@ -344,11 +422,11 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   memset(&A, 0, sizeof(A));
   A.bias = d.bias; A.bias_len = d.cout_pad;
   // pair view (see k_repack_pair): needs pixel pairs to be contiguous in memory
-  const bool pair = k == 3 && s == 2 && x.C == 32 && x.c_stride == 32 && x.W % 2 == 0 && ups == 1 && d.tile_n >= 0;
+  const bool pair_view = k == 3 && s == 2 && x.C == 32 && x.c_stride == 32 && x.W % 2 == 0 && ups == 1 && d.tile_n >= 0;
   int Cin = x.C, cin_pad = d.cin_pad, xW = x.W, x_cs = x.c_stride;
   int kh = k, kw = k, sh = s, sw = s, ph = pad, pw = pad;
   const void* weight = d.weight;
-  if (pair) {
+  if (pair_view) {
     Cin = 64; cin_pad = 64; xW = x.W / 2; x_cs = 64;
     kh = 3; kw = 2; sh = 2; sw = 1; ph = 1; pw = 1;
     const size_t n = (size_t)d.cout_pad * 6 * 64;
@@ -392,20 +470,25 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
     A.tiles_h = (Ho + A.BH - 1) / A.BH;
   }
   const int total_chunks = A.taps * A.kchunks;
+  const long long m_tiles = (long long)A.tiles_w * A.tiles_h * images;
+  // the 2x2 upsample store walks four tensor maps per tile; pairs are not worth it there (tiny layers)
+  const int pair_mode = ups == 2 ? -1 : d.pair;
   if (d.tile_n) {
     A.BN = d.tile_n < 0 ? -d.tile_n : d.tile_n;
     A.resident = 0;
-    if (A.BN == 1) pick_tile(Cout, (long long)A.tiles_w * A.tiles_h * images, total_chunks, A.BK, y_es, &A.BN, &A.resident);
+    A.pair = pair_mode > 0 ? 1 : 0;
+    if (A.BN == 1) pick_tile(Cout, m_tiles, total_chunks, A.BK, y_es, pair_mode, &A.BN, &A.resident, &A.pair);
   } else {
-    pick_tile(Cout, (long long)A.tiles_w * A.tiles_h * images, total_chunks, A.BK, y_es, &A.BN, &A.resident);
+    pick_tile(Cout, m_tiles, total_chunks, A.BK, y_es, pair_mode, &A.BN, &A.resident, &A.pair);
   }
   YB_CHECK_ARG(A.BN == 32 || A.BN == 64 || A.BN == 128 || A.BN == 256, "conv(tc): tile_n must be 32/64/128/256");
+  const int bn_cta = A.pair ? A.BN / 2 : A.BN;
   A.tiles_n = (Cout + A.BN - 1) / A.BN;
   A.n_store_maps = ups == 2 ? 4 : 1;
   A.tmem_cols = 2 * A.BN < 32 ? 32 : 2 * A.BN;   // double-buffered accumulators (64/128/256/512 columns)
-  A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)((A.pair ? 256 : 128) >> 4) << 24);
   // stages / shared memory
-  const size_t a_stage = (size_t)128 * A.BK * 2, b_tile = (size_t)A.BN * A.BK * 2;
+  const size_t a_stage = (size_t)128 * A.BK * 2, b_tile = (size_t)bn_cta * A.BK * 2;
   const size_t stage_bytes = A.resident ? a_stage : a_stage + b_tile;
   // output staging ring: deep enough to overlap the TMA store of one round with the next round's math, as long
   // as the operand pipeline keeps at least 4 stages
@@ -415,7 +498,7 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   int ring = 2;
   size_t fixed = 0;
   for (; ring >= 1; --ring) {
-    fixed = tile_smem(A.BN, A.BK, y_es, A.resident != 0, total_chunks, 0, ring);
+    fixed = tile_smem(A.BN, A.BK, y_es, A.resident != 0, total_chunks, 0, ring, bn_cta);
     if (ring == 1) break;
     if (fixed >= 226 * 1024) continue;
     const int st = (int)((226 * 1024 - fixed) / stage_bytes);
@@ -458,7 +541,7 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   {
     uint64_t dims[3] = {(uint64_t)cin_pad, (uint64_t)A.taps, (uint64_t)d.cout_pad};
     uint64_t str[2] = {(uint64_t)cin_pad * 2, (uint64_t)cin_pad * 2 * A.taps};
-    uint32_t box[3] = {(uint32_t)A.BK, 1, (uint32_t)A.BN};
+    uint32_t box[3] = {(uint32_t)A.BK, 1, (uint32_t)bn_cta};     // pair mode: each CTA loads half of the N tile
     rc = encode(&A.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, weight, dims, str, box, one4, sw_in, "weights");
     if (rc) { delete P; return rc; }
   }
@@ -490,11 +573,14 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
     }
   }
   YB_CHECK_ARG(y.H == Ho * ups && y.W == Wo * ups && y.N == x.N, "conv(tc): output spatial dims mismatch");
-  const long long grid = (long long)A.tiles_n * A.tiles_w * A.tiles_h * images;
-  YB_CHECK_ARG(grid < 0x7fffffffLL, "conv(tc): grid too large");
-  A.total_tiles = (int)grid;
-  P->grid = (int)(grid < num_sms() ? grid : num_sms());
-  if (A.resident) P->grid = P->grid / A.tiles_n * A.tiles_n;
+  const long long units = (long long)A.tiles_n * (A.pair ? (m_tiles + 1) / 2 : m_tiles);
+  YB_CHECK_ARG(units < 0x3fffffffLL, "conv(tc): grid too large");
+  A.total_tiles = (int)units;
+  const int walkers_max = A.pair ? num_sms() / 2 : num_sms();
+  int walkers = (int)(units < walkers_max ? units : walkers_max);
+  if (A.resident) walkers = walkers / A.tiles_n * A.tiles_n;
+  YB_CHECK_ARG(walkers >= 1, "conv(tc): no walker fits the resident layout");
+  P->grid = A.pair ? 2 * walkers : walkers;
   *out = P;
   return YB_OK;
 }
@@ -502,10 +588,12 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
 int conv_tc_launch(const ConvTcPlan* P, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    YB_CUDA(cudaFuncSetAttribute(k_conv_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    YB_CUDA(cudaFuncSetAttribute(k_conv_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    YB_CUDA(cudaFuncSetAttribute(k_conv_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  YB_CUDA(launch_pdl(k_conv_tc, P->grid, kTcThreads, P->smem, s, P->args));
+  if (P->args.pair) YB_CUDA(launch_pdl_pairs(k_conv_tc<true>, P->grid, kTcThreads, P->smem, s, P->args));
+  else YB_CUDA(launch_pdl(k_conv_tc<false>, P->grid, kTcThreads, P->smem, s, P->args));
   return YB_OK;
 }
 

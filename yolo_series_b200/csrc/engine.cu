@@ -108,7 +108,7 @@ extern "C" int yb_engine_create(const yb_tensor* tensors, int n_tensors, const y
     d.x = e->tensors[o.in0]; d.y = e->tensors[o.out0];
     d.weight = e->weights[o.weight]; d.bias = e->biases[o.weight];
     d.cin_pad = o.cin_pad; d.cout_pad = o.cout_pad; d.k = o.k; d.stride = o.stride; d.act = o.act;
-    d.leaky_slope = o.leaky_slope; d.upsample = o.upsample; d.tile_n = o.tile_n; d.stages = o.stages;
+    d.leaky_slope = o.leaky_slope; d.upsample = o.upsample; d.tile_n = o.tile_n; d.stages = o.stages; d.pair = o.pair;
     int rc = d.tile_n < 0 ? YB_ERR_UNSUPPORTED : conv3_tc_plan_create(d, &e->plans3[i]);
     if (rc == YB_ERR_UNSUPPORTED && d.tile_n >= 0) rc = conv3s2p_plan_create(d, &e->plans_s2p[i]);
     if (rc == YB_ERR_UNSUPPORTED) {

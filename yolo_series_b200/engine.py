@@ -118,7 +118,8 @@ class Engine:
                 o.k, o.stride, o.act, o.leaky_slope = fc.k, fc.s, fc.act, fc.slope
                 o.cin_pad, o.cout_pad = cin_pad, fc.c_out
                 if tile_overrides and op.name in tile_overrides:
-                    o.tile_n, o.stages = tile_overrides[op.name]
+                    ov = tuple(tile_overrides[op.name]) + (0,)
+                    o.tile_n, o.stages, o.pair = ov[0], ov[1], ov[2]
                 if op is stem_op:
                     o.kind, o.in0, o.tile_n = OP_STEM, len(self.views) - 1, int(L.reorg)
         tens_c = (_lib.Tensor * len(self.views))()

@@ -17,7 +17,7 @@ def pack_weight(w, cin_pad, dtype):
 
 
 def conv2d(x, w, b, stride=1, act=ACT_NONE, slope=0.0, upsample=1, out=None, out_c_off=0, out_dtype=None,
-           tile_n=0, stages=0):
+           tile_n=0, stages=0, pair=0):
     """x: (N,H,W,Cx) NHWC cuda tensor (bf16 -> tcgen05 path, fp32 -> reference-mode path);
     w: (Cout, Cin, k, k) fp32 with Cin <= Cx; b: (Cout,) fp32."""
     L = _lib.lib()
@@ -38,7 +38,7 @@ def conv2d(x, w, b, stride=1, act=ACT_NONE, slope=0.0, upsample=1, out=None, out
     d.weight, d.bias = wp.data_ptr(), bp.data_ptr()
     d.cin_pad, d.cout_pad, d.k, d.stride = cin_pad, co, k, stride
     d.act, d.leaky_slope, d.upsample = act, slope, upsample
-    d.tile_n, d.stages = tile_n, stages
+    d.tile_n, d.stages, d.pair = tile_n, stages, pair
     _lib.check(L.yb_conv2d(C.byref(d), _lib.stream_ptr()), 'yb_conv2d')
     return out
 
