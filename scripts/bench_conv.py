@@ -1,5 +1,5 @@
 """Micro-benchmark of single conv shapes through yb_conv2d-equivalent engine plans.
-Usage: python scripts/bench_conv.py "Cin,Cout,k,s,H[,tile_n[,stages]]" ... (B=32 fixed unless YB_B set)"""
+Usage: python scripts/bench_conv.py "Cin,Cout,k,s,H[,tile_n[,stages[,pair]]]" ... (B=32 fixed unless YB_B set)"""
 import ctypes as C
 import os
 import sys
@@ -17,6 +17,7 @@ for spec in sys.argv[1:]:
     ci, co, k, s, h = v[:5]
     tile_n = v[5] if len(v) > 5 else 0
     stages = v[6] if len(v) > 6 else 0
+    pair = v[7] if len(v) > 7 else 0
     cx = max(ci, 16)
     x = (torch.randn((B, h, h, cx), device='cuda') * 0.5).bfloat16()
     w = torch.randn((co, ci, k, k)) / (ci * k * k) ** 0.5
@@ -29,7 +30,7 @@ for spec in sys.argv[1:]:
     d.x, d.y = _lib.view(x), _lib.view(out, 0, co)
     d.weight, d.bias = wp.data_ptr(), bp.data_ptr()
     d.cin_pad, d.cout_pad, d.k, d.stride, d.act, d.upsample = cx, co, k, s, 1, 1
-    d.tile_n, d.stages = tile_n, stages
+    d.tile_n, d.stages, d.pair = tile_n, stages, pair
     plan = C.c_void_p()
     _lib.check(L.yb_conv_plan_create(C.byref(d), C.byref(plan)))
     for _ in range(3):

@@ -352,6 +352,14 @@ static void pick_tile(int cout, long long m_tiles, int chunks, int bk, int y_es,
   const int force = force_env ? atoi(force_env) : -1;
   static const char* pair_env = getenv("YB_PAIR");        // tuning aid: overrides a pair_mode of 0
   if (pair_mode == 0 && pair_env) pair_mode = atoi(pair_env);
+  if (pair_mode == 0) {
+    // Measured on the yolov7 shapes at batch 32 (scripts/pair_sweep_specs.txt, profiles/round2_pair_sweep.txt): pairs win
+    // 5-12 % where the K loop is long (1x1 with Cin >= 1024, stride-2 3x3 with Cin >= 128) and lose 5-30 % on short-K
+    // layers, where the extra cluster handshakes are not amortised; with fewer tiles than SMs they only pay off for
+    // very long K.
+    const long long k_total = (long long)chunks * bk;
+    pair_mode = (k_total >= 1024 && (k_total >= 4096 || m_tiles >= num_sms())) ? 1 : -1;
+  }
   int best = 64, best_res = 0, best_pair = 0;
   double best_cost = 1e30;
   for (int pr = 0; pr < 2; ++pr) {
