@@ -130,13 +130,16 @@ def test_stage_input_and_reorg():
 @pytest.mark.parametrize('cfg', [(3, 32, 1, False, 48, 160), (3, 32, 2, False, 64, 200), (3, 64, 1, True, 64, 96),
                                  (3, 80, 1, True, 32, 288), (3, 32, 1, False, 37, 70), (3, 32, 2, False, 45, 75),
                                  (3, 32, 1, False, 256, 320), (3, 32, 2, False, 256, 640), (3, 32, 1, False, 37, 72),
-                                 (3, 32, 2, False, 45, 76)],
+                                 (3, 32, 2, False, 45, 76), (3, 64, 1, True, 256, 1280), (3, 80, 1, True, 130, 520),
+                                 (3, 64, 1, True, 64, 100), (3, 80, 1, True, 2, 8)],
                          ids=['v7', 'tiny_s2', 'w6_reorg', 'e6e_reorg', 'v7_ragged', 'tiny_ragged', 'v7_ringwrap',
-                              'tiny_ringwrap', 'v7_ragged4', 'tiny_ragged4'])
+                              'tiny_ringwrap', 'v7_ragged4', 'tiny_ragged4', 'w6_reorg_ringwrap', 'e6e_reorg_ragged',
+                              'w6_reorg_w_not_mult8_fallback', 'e6e_reorg_single_row'])
 @pytest.mark.parametrize('u8', [True, False])
 def test_stem_conv_fused_staging(cfg, u8):
-    """Fused staging + first conv (tcgen05 kernel for RGB -> 32, mma.sync kernel for the ReOrg stems) vs fp32
-    conv of the bf16-rounded operands."""
+    """Fused staging + first conv (tcgen05 kernels: k_stem_tc for RGB -> 32, k_stemr_tc for the ReOrg stems 12 -> 64 | 80;
+    the mma.sync kernel remains for image widths the builders cannot load in aligned groups) vs fp32 conv of the
+    bf16-rounded operands."""
     from yolo_series_b200 import ops
     C_, Co, s, reorg, H, W = cfg
     g = torch.Generator().manual_seed(6)

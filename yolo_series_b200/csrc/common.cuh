@@ -129,4 +129,8 @@ void conv3s2p_plan_destroy(ConvS2pPlan* p);
 int stem_tc_launch(const void* img, int img_u8, int B, int H, int W, const void* weight, const float* bias,
                    int cin_pad, int stride, int act, float slope, const yb_tensor* y, cudaStream_t st);
 
+// tcgen05 first layer of the P6 cfgs: ReOrg + 12 -> 64 | 80 (stemr_tc.cu); YB_ERR_UNSUPPORTED -> mma.sync stem
+int stemr_tc_launch(const void* img, int img_u8, int B, int H, int W, const void* weight, const float* bias,
+                    int cin_pad, int stride, int act, float slope, const yb_tensor* y, cudaStream_t st);
+
 }  // namespace yb

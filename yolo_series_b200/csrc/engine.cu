@@ -173,7 +173,9 @@ extern "C" const char* yb_engine_op_kernel(const yb_engine* e, int i) {
       const yb_tensor& im = e->tensors[o.in0];
       const yb_tensor& y = e->tensors[o.out0];
       const bool tc = !o.tile_n && im.C == 3 && y.C == 32 && im.W % 4 == 0 && (uintptr_t)im.data % 16 == 0;
-      return tc ? "k_stem_tc" : "k_stem";
+      const bool tcr = o.tile_n && im.C == 3 && (y.C == 64 || y.C == 80) && o.stride == 1 && im.W % 8 == 0 &&
+                       im.H % 2 == 0 && (uintptr_t)im.data % 16 == 0 && getenv("YB_STEM_MMA_SYNC") == nullptr;
+      return tc ? "k_stem_tc" : tcr ? "k_stemr_tc" : "k_stem";
     }
     case YB_OP_MAXPOOL2: return "k_maxpool2";
     case YB_OP_POOL_S1: return "k_pool_s1";

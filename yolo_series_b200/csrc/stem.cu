@@ -265,6 +265,11 @@ extern "C" int yb_stem_conv(const void* img, int img_dtype, int B, int C, int H,
     const int rc = stem_tc_launch(img, P.img_u8, B, H, W, weight, bias, cin_pad, stride, act, leaky_slope, y, st);
     if (rc != YB_ERR_UNSUPPORTED) return rc;
   }
+  static const bool no_tc = getenv("YB_STEM_MMA_SYNC") != nullptr;   // tuning / comparison aid: force the mma.sync stem
+  if (reorg && C == 3 && !no_tc) {   // ReOrg first layer of the P6 cfgs: tcgen05 kernel (stemr_tc.cu)
+    const int rc = stemr_tc_launch(img, P.img_u8, B, H, W, weight, bias, cin_pad, stride, act, leaky_slope, y, st);
+    if (rc != YB_ERR_UNSUPPORTED) return rc;
+  }
   const int nt = P.Cout / 16;
   if (P.CP == 8 && stride == 1 && nt == 2) return launch_stem<2, 8, 1, false>(P, st);
   if (P.CP == 8 && stride == 2 && nt == 2) return launch_stem<2, 8, 2, false>(P, st);
