@@ -81,7 +81,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
                  "r"((uint32_t)G.tmem_cols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  for (int i = threadIdx.x; i < kMaxBias; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
+  {   // bias of the channels this launch can touch (the last N tile may reach past Cout: zeros there)
+    const int nb = min(kMaxBias, (G.bias_len + 255) & ~255);
+    for (int i = threadIdx.x; i < nb; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
+  }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -196,7 +199,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
         }
       }
     }
-    if (store_thread) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem may go once it has been read; the writes complete with the grid
   }
   __syncthreads();
   if (warp == 1) {

@@ -101,7 +101,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
       asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
   }
-  for (int i = threadIdx.x; i < kMaxBias; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
+  {   // bias of the channels this launch can touch (the last N tile may reach past Cout: zeros there)
+    const int nb = min(kMaxBias, (G.bias_len + 255) & ~255);
+    for (int i = threadIdx.x; i < nb; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
+  }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   if (PAIR) cluster_sync_all();     // the peer's barriers must exist before anything signals them
   else __syncthreads();
@@ -297,7 +300,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     if (G.act == YB_ACT_SILU) run(std::integral_constant<int, YB_ACT_SILU>{});
     else if (G.act == YB_ACT_LEAKY) run(std::integral_constant<int, YB_ACT_LEAKY>{});
     else run(std::integral_constant<int, YB_ACT_NONE>{});
-    if ((ew & 3) == 0 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if ((ew & 3) == 0 && lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem may go once it has been read; the writes complete with the grid
   }
   if (PAIR) {
     // neither CTA may leave (or free TMEM) while the other can still signal its barriers or read its operands
