@@ -41,7 +41,18 @@ struct ConvTcArgs {
   int total_tiles;                 // work units: (m, n) tiles, or (pair of m tiles, n) in pair mode
   int pair;                        // 1: CTA pairs (clusters of 2, tcgen05 cta_group::2, M = 256 per MMA)
   uint32_t idesc;
+  unsigned long long* dbg;         // tuning aid (env YB_CONV_TS = device address): globaltimer stamps of CTA 0
 };
+
+// stamp `slot` from one thread of CTA 0 when the debug buffer is set (scripts/conv_timeline.py)
+#define YB_CTS(slot, cond)                                                                                  \
+  do {                                                                                                      \
+    if (G.dbg && blockIdx.x == 0 && (cond)) {                                                               \
+      unsigned long long t_;                                                                                \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                \
+      G.dbg[slot] = t_;                                                                                     \
+    }                                                                                                       \
+  } while (0)
 
 // Persistent kernel: one CTA per SM walks tiles t = blockIdx.x, +gridDim.x, ...  The TMA producer runs
 // ahead across tile boundaries (smem ring of `stages` K-chunks), accumulators are double-buffered in
@@ -58,6 +69,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
   const bool leader = rank == 0u;
+  YB_CTS(0, threadIdx.x == 0);
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
   unsigned char* tiles_ptr = smem_dyn + (tiles - raw);
@@ -136,8 +148,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     }
     __syncwarp();
   }
+  YB_CTS(1, threadIdx.x == 0);
   pdl_launch_dependents();   // set-up done: the next kernel's CTAs may take SMs as ours retire
   pdl_wait();                // activations written by the previous kernel are visible from here on
+  YB_CTS(2, threadIdx.x == 0);
 
   if (warp == 0) {
     // ================================ TMA producer ================================
@@ -172,6 +186,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
             }
           }
           __syncwarp();
+          YB_CTS(3, lane == 0 && t == t_first && tap == 0 && kk == 0);
           if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
         }
         if (++dx == G.kw) { dx = 0; ++dy; }
@@ -197,6 +212,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
       const uint32_t tmem_d = tmem_base + acc * (uint32_t)G.BN;
       for (int c = 0; c < total_chunks; ++c) {
         mbar_wait(bar_full0 + 8u * s, ph);
+        YB_CTS(4, lane == 0 && it == 0 && c == 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t da = ((ring + s * stage_bytes) >> 4) & 0x3FFF;
         const uint32_t db = G.resident ? bres + (uint32_t)c * bstep : da + boff;
@@ -231,6 +247,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
       }
       if (elect_one()) { if (PAIR) umma_commit_2sm(bar_tfull0 + 8u * acc); else umma_commit(bar_tfull0 + 8u * acc); }
       __syncwarp();
+      YB_CTS(5, lane == 0 && it == 0);
     }
     }
   } else {
@@ -268,6 +285,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
         const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
         const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
         mbar_wait(bar_tfull0 + 8u * acc, aph);
+        YB_CTS(6, store_thread && it == 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         // the slot's previous stores (issued a whole tile ago by this store thread) must have read it
         if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -294,6 +312,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
             for (int g = 0; g < ngroups; ++g)
               tma_store_4d(&G.tm_y[mp], sbase + (uint32_t)g * 16384u, n0 + g * per_group, w0, G.flat ? 0 : h0, img);
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          YB_CTS(7, it == 0);
         }
       }
     };
@@ -301,6 +320,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     else if (G.act == YB_ACT_LEAKY) run(std::integral_constant<int, YB_ACT_LEAKY>{});
     else run(std::integral_constant<int, YB_ACT_NONE>{});
     if ((ew & 3) == 0 && lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem may go once it has been read; the writes complete with the grid
+    YB_CTS(8, warp == 2 && lane == 0);
   }
   if (PAIR) {
     // neither CTA may leave (or free TMEM) while the other can still signal its barriers or read its operands
@@ -319,6 +339,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G.tmem_cols)
                  : "memory");
   }
+  YB_CTS(9, threadIdx.x == 32);
 }
 
 struct ConvTcPlan {
@@ -432,6 +453,7 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   ConvTcArgs& A = P->args;
   memset(&A, 0, sizeof(A));
   A.bias = d.bias; A.bias_len = d.cout_pad;
+  if (const char* ts = getenv("YB_CONV_TS")) A.dbg = reinterpret_cast<unsigned long long*>(strtoull(ts, nullptr, 0));
   // pair view (see k_repack_pair): needs pixel pairs to be contiguous in memory
   const bool pair_view = k == 3 && s == 2 && x.C == 32 && x.c_stride == 32 && x.W % 2 == 0 && ups == 1 && d.tile_n >= 0;
   int Cin = x.C, cin_pad = d.cin_pad, xW = x.W, x_cs = x.c_stride;
