@@ -493,8 +493,9 @@ def main():
             tp = os.path.join(ROOT, 'profiles', 'round2_launch_summary.json')
             if not os.path.exists(tp):
                 tp = os.path.join(ROOT, 'profiles', 'round1_launch_summary.json')
-            for k in json.load(open(tp))['kernels']:
-                traffic[k['kernel'].split('<')[0]] = k['dram_bytes']
+            for k in json.load(open(tp))['kernels']:        # template instances (k_conv_tc<0> / <1>) add up
+                base = k['kernel'].split('<')[0]
+                traffic[base] = traffic.get(base, 0) + k['dram_bytes']
             traffic_src = os.path.relpath(tp, ROOT) + ' (ncu dram__bytes_read+write summed over the kernel\'s launches of one step)'
         except Exception:  # noqa: BLE001
             pass
