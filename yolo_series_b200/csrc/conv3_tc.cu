@@ -24,6 +24,7 @@ struct Conv3Args {
   const float* bias;
   int tiles_n, tiles_w, tiles_h;   // super-tile grid per image
   int BW, BH, BN, BK;
+  int nsub;                        // sub-tiles per CTA tile: 2 (super-tile, weights shared) or 1 (grids short of CTAs)
   int kchunks, stages;
   int act; float slope;
   int sw_mode, tmem_cols, bias_len, total_tiles;
@@ -32,13 +33,13 @@ struct Conv3Args {
   uint32_t idesc;
 };
 
-// 18 * NK MMAs of one pipeline stage: 2 sub-tiles x 3 filter rows x NK 16-wide K steps.
-template <int NK>
+// NSUB * 3 * NK MMAs of one pipeline stage: NSUB sub-tiles x 3 filter rows x NK 16-wide K steps.
+template <int NK, int NSUB>
 __device__ __forceinline__ void issue_stage(uint32_t tmem_d0, uint32_t bn, uint32_t dlo, uint32_t hi32,
                                             const uint32_t (&aoff)[2][3], const uint32_t (&boff)[3],
                                             uint32_t idesc, uint32_t acc0) {
 #pragma unroll
-  for (int j = 0; j < 2; ++j) {
+  for (int j = 0; j < NSUB; ++j) {
 #pragma unroll
     for (int dy = 0; dy < 3; ++dy) {
 #pragma unroll
@@ -105,7 +106,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
       const int img = m_tile / tiles_m_per_img;
       m_tile -= img * tiles_m_per_img;
       const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
-      const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * 2 * G.BH;
+      const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.nsub * G.BH;
       for (int kk = 0; kk < G.kchunks; ++kk) {
 #pragma unroll
         for (int dx = 0; dx < 3; ++dx) {
@@ -150,8 +151,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t dlo = ((tiles + s * stage_bytes) >> 4) & 0x3FFF;
         if (elect_one()) {
-          if (nk == 4) issue_stage<4>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, (uint32_t)(c != 0));
-          else         issue_stage<2>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, (uint32_t)(c != 0));
+          const uint32_t acc0 = (uint32_t)(c != 0);
+          if (G.nsub == 2) {
+            if (nk == 4) issue_stage<4, 2>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+            else         issue_stage<2, 2>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+          } else {
+            if (nk == 4) issue_stage<4, 1>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+            else         issue_stage<2, 1>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+          }
           umma_commit(bar_empty0 + 8u * s);
         }
         __syncwarp();
@@ -179,10 +186,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
       const int img = m_tile / tiles_m_per_img;
       m_tile -= img * tiles_m_per_img;
       const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
-      const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * 2 * G.BH;
+      const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.nsub * G.BH;
       mbar_wait(bar_tfull0 + 8u * par, aph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      for (int j = 0; j < 2; ++j) {
+      for (int j = 0; j < G.nsub; ++j) {
         if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging free again
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (par * 2u + (uint32_t)j) * (uint32_t)G.BN;
@@ -191,7 +198,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
         if (store_thread) {
-          if (j == 1) mbar_arrive(bar_tempty0 + 8u * par);   // both sub-accumulators have been read
+          if (j == G.nsub - 1) mbar_arrive(bar_tempty0 + 8u * par);   // all sub-accumulators have been read
           const int ngroups = (G.BN + 63) / 64;
           for (int g = 0; g < ngroups; ++g)
             tma_store_4d(&G.tm_y, staging + (uint32_t)g * 16384u, n0 + g * 64, w0, h0 + j * G.BH, img);
@@ -235,36 +242,54 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
   A.kchunks = (Cin + A.BK - 1) / A.BK;
   A.sw_mode = A.BK == 64 ? 2 : 4;
   const CUtensorMapSwizzle sw_in = A.BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
-  // ---- spatial tile: BW multiple of 8, BH = 128 / BW (sub-tile <= 128 px), super-tile BW x 2BH
-  long long best_cost = -1;
+  // ---- tile shape: spatial sub-tile BW x BH (BW multiple of 8, BH = 128 / BW), NSUB stacked sub-tiles per CTA tile,
+  // N tile.  The super-tile (NSUB = 2) shares every weight tile between two sub-tiles, N = 128 halves the activation
+  // traffic of N = 64 -- but at small maps / small batches such tiles are fewer than the SMs (512 -> 512 at 20 x 20,
+  // batch 8: 52 CTAs of 19 us each), so the shape is chosen by an estimate of the whole launch:
+  //   rounds of the persistent grid x stages x max(MMA cycles, operand bytes / 42 B/clk of L2 -> smem) + fill / drain.
   const int bw_step = A.BK == 64 ? 8 : 16;   // sub-tile / filter-row offsets stay 1024-byte aligned
-  for (int bw = bw_step; bw <= 128; bw += bw_step) {
-    int bh = 128 / bw;
-    if (bh < 1) continue;
-    if (2 * bh + 2 > 256) continue;
-    const long long nt = (long long)((W + bw - 1) / bw) * ((H + 2 * bh - 1) / (2 * bh));
-    const long long cost = nt * ((2 * bh + 2) * bw + 96);   // slab rows (+ weight rows equivalent) per super-tile
-    if (best_cost < 0 || cost < best_cost) { best_cost = cost; A.BW = bw; A.BH = bh; }
+  const uint32_t row_bytes = A.BK * 2;
+  static const char* nsub_env = getenv("YB_C3_NSUB");       // tuning aids
+  const int nsub_force = nsub_env ? atoi(nsub_env) : 0;
+  double best_time = 1e30;
+  for (int nsub = 2; nsub >= 1; --nsub) {
+    if (nsub_force && nsub != nsub_force) continue;
+    long long best_cost = -1;
+    int cbw = 0, cbh = 0;
+    for (int bw = bw_step; bw <= 128; bw += bw_step) {
+      const int bh = 128 / bw;
+      if (bh < 1 || nsub * bh + 2 > 256) continue;
+      const long long nt = (long long)((W + bw - 1) / bw) * ((H + nsub * bh - 1) / (nsub * bh));
+      const long long cost = nt * ((nsub * bh + 2) * bw + 96);   // slab rows (+ weight rows equivalent) per tile
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; cbw = bw; cbh = bh; }
+    }
+    const long long m_tiles = (long long)((W + cbw - 1) / cbw) * ((H + nsub * cbh - 1) / (nsub * cbh)) * x.N;
+    const int bn_cands[3] = {128, 64, 32};
+    for (int bi = 0; bi < 3; ++bi) {
+      const int bn = bn_cands[bi];
+      if (d.tile_n ? bn != d.tile_n : ((bn == 32) != (Cout <= 32) || (bn == 128 && Cout <= 64))) continue;
+      const int tiles_n = (Cout + bn - 1) / bn;
+      const long long tiles = m_tiles * tiles_n;
+      const long long grid = tiles < num_sms() ? tiles : num_sms();
+      const double rounds = (double)((tiles + grid - 1) / grid);
+      const double mma = nsub * 3 * (A.BK / 16) * (bn >= 128 ? 64.0 : bn == 64 ? 48.0 : 40.0);   // N <= 64: smem-operand bound
+      const double load = ((double)(nsub * cbh + 2) * cbw + 3.0 * bn) * row_bytes / 42.0;
+      const double t = rounds * 3 * A.kchunks * (mma > load ? mma : load) + nsub * (bn * 10.0 + 600.0) + 3000.0;
+      if (t < best_time * 0.97) {   // prefer the larger shape unless the smaller one clearly wins
+        best_time = t; A.nsub = nsub; A.BW = cbw; A.BH = cbh; A.BN = bn;
+      }
+    }
   }
+  YB_CHECK_ARG(A.nsub && (A.BN == 32 || A.BN == 64 || A.BN == 128), "conv3(tc): tile_n must be 32/64/128");
   A.tiles_w = (W + A.BW - 1) / A.BW;
-  A.tiles_h = (H + 2 * A.BH - 1) / (2 * A.BH);
-  if (d.tile_n) A.BN = d.tile_n;
-  else if (Cout <= 32) A.BN = 32;
-  else if (Cout <= 64) A.BN = 64;
-  else {
-    // 64 vs 128: fewer padded columns wins, ties -> 128 (halves the activation traffic)
-    const int c64 = (Cout + 63) / 64 * 64, c128 = (Cout + 127) / 128 * 128;
-    A.BN = c64 < c128 ? 64 : 128;
-  }
-  YB_CHECK_ARG(A.BN == 32 || A.BN == 64 || A.BN == 128, "conv3(tc): tile_n must be 32/64/128");
+  A.tiles_h = (H + A.nsub * A.BH - 1) / (A.nsub * A.BH);
   A.tiles_n = (Cout + A.BN - 1) / A.BN;
   A.tmem_cols = 4 * A.BN < 32 ? 32 : 4 * A.BN;
   A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-  const uint32_t row_bytes = A.BK * 2;
-  A.a_tx = (uint32_t)(2 * A.BH + 2) * A.BW * row_bytes;
-  // the last sub-tile's MMA reads 128 rows from row (BH+2)*BW: keep those reads inside the stage
-  uint32_t need_rows = (uint32_t)((A.BH + 2) * A.BW + 128);
-  uint32_t slab_rows = (uint32_t)(2 * A.BH + 2) * A.BW;
+  A.a_tx = (uint32_t)(A.nsub * A.BH + 2) * A.BW * row_bytes;
+  // the last sub-tile's MMA (filter row 2) reads 128 rows from row ((NSUB-1)*BH + 2)*BW: keep those reads inside the stage
+  uint32_t need_rows = (uint32_t)(((A.nsub - 1) * A.BH + 2) * A.BW + 128);
+  uint32_t slab_rows = (uint32_t)(A.nsub * A.BH + 2) * A.BW;
   if (need_rows > slab_rows) slab_rows = need_rows;
   A.a_bytes = (uint32_t)align_up((size_t)slab_rows * row_bytes, 1024);
   const size_t stage_bytes = (size_t)A.a_bytes + 3 * (size_t)A.BN * row_bytes;
@@ -282,7 +307,7 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
     const uint64_t cs = (uint64_t)x.c_stride * 2;
     uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)x.N};
     uint64_t str[3] = {cs, cs * W, cs * W * H};
-    uint32_t box[4] = {(uint32_t)A.BK, (uint32_t)A.BW, (uint32_t)(2 * A.BH + 2), 1};
+    uint32_t box[4] = {(uint32_t)A.BK, (uint32_t)A.BW, (uint32_t)(A.nsub * A.BH + 2), 1};
     rc = encode(&A.tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x.data, dims, str, box, one4, sw_in, "conv3 activations");
     if (rc) { delete P; return rc; }
   }
