@@ -209,3 +209,35 @@ def test_conv_tc_cta_pairs(case):
     # fp32 output (head logits) through the pair path
     y3 = ops.conv2d(xd, w, b, s, act, 0.1, 1, tile_n=tn if tn > -256 else -128, pair=1, out_dtype=torch.float32)
     assert torch.allclose(_nchw(y3[..., :Co].cpu()), ref, rtol=1.2e-2, atol=1.2e-2)
+
+
+SLAB_PAIR_CASES = [
+    # (N, H, W, Cin, Cout, act, tile_n): 3x3 stride-1 layers through the slab kernel (tile_n >= 0)
+    (1, 160, 160, 64, 64, 1, 0),          # the smem-operand-bound N = 64 layer class the pairs are for; many rounds
+    (2, 40, 40, 128, 128, 1, 0),          # N = 128 -> 64 weight rows per CTA
+    (1, 80, 80, 64, 192, 1, 64),          # three N tiles
+    (1, 40, 40, 32, 32, 2, 0),            # Cin 32 (SW64), N = 32 -> 16 weight rows per CTA, LeakyReLU
+    (3, 12, 20, 96, 96, 1, 0),            # ragged tiles, odd number of M tiles: the last pair has a tile past the end
+    (2, 24, 24, 512, 64, 1, 0),           # 8 K chunks
+    (1, 8, 8, 64, 64, 1, 0),              # a single tile
+]
+
+
+@pytest.mark.parametrize('case', SLAB_PAIR_CASES, ids=[str(c) for c in SLAB_PAIR_CASES])
+def test_conv3_slab_cta_pairs(case):
+    """k_conv3_tc<PAIR>: the slab kernel as clusters of two CTAs (cta_group::2, M = 256, half of every weight tile per
+    CTA): bit-identical to the single-CTA slab kernel, within bf16 tolerance of the fp32 PyTorch reference."""
+    from yolo_series_b200 import ops
+    N, H, W, Ci, Co, act, tn = case
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn((N, Ci, H, W), generator=g).bfloat16().float()
+    w = (torch.randn((Co, Ci, 3, 3), generator=g) / (Ci * 9) ** 0.5).bfloat16().float()
+    b = torch.randn((Co,), generator=g)
+    ref = _ref_conv(x, w, b, 1, act, 0.1, 1)
+    xd = _nhwc(x).cuda().bfloat16()
+    y1 = ops.conv2d(xd, w, b, 1, act, 0.1, 1, tile_n=tn, pair=-1)
+    y2 = ops.conv2d(xd, w, b, 1, act, 0.1, 1, tile_n=tn, pair=1)
+    torch.cuda.synchronize()
+    got = _nchw(y2[..., :Co].float().cpu())
+    assert torch.allclose(got, ref, rtol=1.2e-2, atol=1.2e-2), float((got - ref).abs().max())
+    assert torch.equal(y1, y2)

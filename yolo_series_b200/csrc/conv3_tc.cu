@@ -27,14 +27,15 @@ struct Conv3Args {
   int nsub;                        // sub-tiles per CTA tile: 2 (super-tile, weights shared) or 1 (grids short of CTAs)
   int kchunks, stages;
   int act; float slope;
-  int sw_mode, tmem_cols, bias_len, total_tiles;
+  int sw_mode, tmem_cols, bias_len, total_tiles;   // total_tiles = work units: tiles, or (pair of M tiles, N tile)
+  int pair;                        // 1: CTA pairs (cta_group::2): M = 256 per MMA, each CTA holds half of every weight tile
   uint32_t a_bytes;                // slab bytes, rounded up to 1024
   uint32_t a_tx;                   // bytes the slab TMA actually delivers
   uint32_t idesc;
 };
 
 // NSUB * 3 * NK MMAs of one pipeline stage: NSUB sub-tiles x 3 filter rows x NK 16-wide K steps.
-template <int NK, int NSUB>
+template <int NK, int NSUB, bool PAIR>
 __device__ __forceinline__ void issue_stage(uint32_t tmem_d0, uint32_t bn, uint32_t dlo, uint32_t hi32,
                                             const uint32_t (&aoff)[2][3], const uint32_t (&boff)[3],
                                             uint32_t idesc, uint32_t acc0) {
@@ -43,21 +44,32 @@ __device__ __forceinline__ void issue_stage(uint32_t tmem_d0, uint32_t bn, uint3
 #pragma unroll
     for (int dy = 0; dy < 3; ++dy) {
 #pragma unroll
-      for (int k = 0; k < NK; ++k)
-        umma_bf16_lh(tmem_d0 + (uint32_t)j * bn, dlo + aoff[j][dy] + (uint32_t)(2 * k),
-                     dlo + boff[dy] + (uint32_t)(2 * k), hi32, idesc, (dy | k) ? 1u : acc0);
+      for (int k = 0; k < NK; ++k) {
+        if (PAIR) umma_bf16_lh_2sm(tmem_d0 + (uint32_t)j * bn, dlo + aoff[j][dy] + (uint32_t)(2 * k),
+                                   dlo + boff[dy] + (uint32_t)(2 * k), hi32, idesc, (dy | k) ? 1u : acc0);
+        else umma_bf16_lh(tmem_d0 + (uint32_t)j * bn, dlo + aoff[j][dy] + (uint32_t)(2 * k),
+                          dlo + boff[dy] + (uint32_t)(2 * k), hi32, idesc, (dy | k) ? 1u : acc0);
+      }
     }
   }
 }
 
+// PAIR = true (clusters of two CTAs): the pair takes two consecutive M tiles of one N tile; every MMA is one
+// tcgen05.mma.cta_group::2 of M = 256 whose B operand is split between the two CTAs (each loads and reads only BN / 2
+// rows of every weight tile) -- for N <= 64, where the single-CTA MMA is bound by shared-memory operand reads
+// (A 4 KB + B 2 KB per 32 tensor cycles), that takes the B share off each SM.  Protocol: tc_common.cuh "CTA pairs".
+template <bool PAIR>
 __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constant__ Conv3Args G) {
   extern __shared__ unsigned char smem_dyn[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0u;
+  const uint32_t bn_cta = PAIR ? (uint32_t)G.BN / 2u : (uint32_t)G.BN;
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
   unsigned char* tiles_ptr = smem_dyn + (tiles - raw);
   const uint32_t row_bytes = (uint32_t)G.BK * 2u;
-  const uint32_t b_bytes = (uint32_t)G.BN * row_bytes;
+  const uint32_t b_bytes = bn_cta * row_bytes;
   const uint32_t stage_bytes = G.a_bytes + 3u * b_bytes;
   const uint32_t pipe_bytes = stage_bytes * G.stages;
   const uint32_t staging = tiles + pipe_bytes;
@@ -74,22 +86,31 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
     tma_prefetch_desc(&G.tm_b);
     tma_prefetch_desc(&G.tm_y);
     for (int s = 0; s < G.stages; ++s) { mbar_init(bar_full0 + 8u * s, 1); mbar_init(bar_empty0 + 8u * s, 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull0 + 8u * i, 1); mbar_init(bar_tempty0 + 8u * i, 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(bar_tfull0 + 8u * i, 1); mbar_init(bar_tempty0 + 8u * i, PAIR ? 2 : 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"((uint32_t)G.tmem_cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (PAIR) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"((uint32_t)G.tmem_cols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"((uint32_t)G.tmem_cols) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   {   // bias of the channels this launch can touch (the last N tile may reach past Cout: zeros there)
     const int nb = min(kMaxBias, (G.bias_len + 255) & ~255);
     for (int i = threadIdx.x; i < nb; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-  __syncthreads();
+  if (PAIR) cluster_sync_all();     // the peer's barriers must exist before anything signals them
+  else __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
+  const int walker = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int walkers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   pdl_launch_dependents();   // set-up done: the next kernel's CTAs may take SMs as ours retire
   pdl_wait();                // activations written by the previous kernel are visible from here on
   const int tiles_m_per_img = G.tiles_w * G.tiles_h;
@@ -98,11 +119,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
   if (warp == 0) {
     // ================================ TMA producer ================================
     // Warp-uniform control flow, one elected lane issues the copies (coordinates live in uniform registers).
-    const uint32_t tx = G.a_tx + 3u * b_bytes;
+    const uint32_t tx = (PAIR ? 2u : 1u) * (G.a_tx + 3u * b_bytes);   // the leader's barrier collects both CTAs' bytes
     uint32_t s = 0, ph = 1;  // ring slot + parity to wait for on its empty barrier
-    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x) {
+    for (int t = walker; t < G.total_tiles; t += walkers) {
       const int n_tile = t % G.tiles_n;
       int m_tile = t / G.tiles_n;
+      if (PAIR) m_tile = 2 * m_tile + (int)rank;   // a tile past the end loads zeros and stores nothing (TMA clips)
       const int img = m_tile / tiles_m_per_img;
       m_tile -= img * tiles_m_per_img;
       const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
@@ -113,12 +135,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
           mbar_wait(bar_empty0 + 8u * s, ph);
           if (elect_one()) {
             const uint32_t full = bar_full0 + 8u * s;
-            mbar_expect_tx(full, tx);
+            if (leader) mbar_expect_tx(full, tx);
             const uint32_t sa = tiles + s * stage_bytes;
-            tma_load_4d(&G.tm_a, full, sa, kk * G.BK, w0 + dx - 1, h0 - 1, img);
+            if (PAIR) {
+              tma_load_4d_2sm(&G.tm_a, full, sa, kk * G.BK, w0 + dx - 1, h0 - 1, img);
 #pragma unroll
-            for (int dy = 0; dy < 3; ++dy)
-              tma_load_3d(&G.tm_b, full, sa + G.a_bytes + (uint32_t)dy * b_bytes, kk * G.BK, dy * 3 + dx, n0);
+              for (int dy = 0; dy < 3; ++dy)
+                tma_load_3d_2sm(&G.tm_b, full, sa + G.a_bytes + (uint32_t)dy * b_bytes, kk * G.BK, dy * 3 + dx,
+                                n0 + (int)(rank * bn_cta));
+            } else {
+              tma_load_4d(&G.tm_a, full, sa, kk * G.BK, w0 + dx - 1, h0 - 1, img);
+#pragma unroll
+              for (int dy = 0; dy < 3; ++dy)
+                tma_load_3d(&G.tm_b, full, sa + G.a_bytes + (uint32_t)dy * b_bytes, kk * G.BK, dy * 3 + dx, n0);
+            }
           }
           __syncwarp();
           if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
@@ -126,8 +156,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
       }
     }
   } else if (warp == 1) {
-    // ================================ MMA issuer ==================================
+    // ================================ MMA issuer (pair mode: the leader CTA only) ==================================
     // Whole warp runs the (uniform) control flow; one elected lane issues tcgen05.mma / commit.
+    if (leader) {
     const uint32_t sbo = 8u * row_bytes;
     const int nk = G.BK / 16;
     const uint32_t sub_rows = (uint32_t)(G.BH * G.BW);   // rows between the two sub-tiles
@@ -141,9 +172,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
     }
     uint32_t s = 0, ph = 0;
     int it = 0;
-    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
+    for (int t = walker; t < G.total_tiles; t += walkers, ++it) {
       const uint32_t par = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
-      mbar_wait(bar_tempty0 + 8u * par, aph ^ 1u);
+      if (PAIR) mbar_wait_cluster(bar_tempty0 + 8u * par, aph ^ 1u);   // both CTAs' epilogues have drained it
+      else mbar_wait(bar_tempty0 + 8u * par, aph ^ 1u);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t tmem_d0 = tmem_base + (par * 2u) * (uint32_t)G.BN;
       for (int c = 0; c < stages_per_tile; ++c) {
@@ -153,19 +185,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
         if (elect_one()) {
           const uint32_t acc0 = (uint32_t)(c != 0);
           if (G.nsub == 2) {
-            if (nk == 4) issue_stage<4, 2>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
-            else         issue_stage<2, 2>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+            if (nk == 4) issue_stage<4, 2, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+            else         issue_stage<2, 2, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
           } else {
-            if (nk == 4) issue_stage<4, 1>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
-            else         issue_stage<2, 1>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+            if (nk == 4) issue_stage<4, 1, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+            else         issue_stage<2, 1, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
           }
-          umma_commit(bar_empty0 + 8u * s);
+          if (PAIR) umma_commit_2sm(bar_empty0 + 8u * s); else umma_commit(bar_empty0 + 8u * s);
         }
         __syncwarp();
         if (++s == (uint32_t)G.stages) { s = 0; ph ^= 1u; }
       }
-      if (elect_one()) umma_commit(bar_tfull0 + 8u * par);
+      if (elect_one()) { if (PAIR) umma_commit_2sm(bar_tfull0 + 8u * par); else umma_commit(bar_tfull0 + 8u * par); }
       __syncwarp();
+    }
     }
   } else {
     // ================================ epilogue ====================================
@@ -179,10 +212,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
     const int c_end = half == 0 ? (nchunks + 1) / 2 : nchunks;
     const bool store_thread = (warp == 2 && lane == 0);
     int it = 0;
-    for (int t = blockIdx.x; t < G.total_tiles; t += gridDim.x, ++it) {
+    for (int t = walker; t < G.total_tiles; t += walkers, ++it) {
       const uint32_t par = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
       const int n_tile = t % G.tiles_n;
       int m_tile = t / G.tiles_n;
+      if (PAIR) m_tile = 2 * m_tile + (int)rank;   // a tile past the end loads zeros and stores nothing (TMA clips)
       const int img = m_tile / tiles_m_per_img;
       m_tile -= img * tiles_m_per_img;
       const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
@@ -198,7 +232,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
         if (store_thread) {
-          if (j == G.nsub - 1) mbar_arrive(bar_tempty0 + 8u * par);   // all sub-accumulators have been read
+          if (j == G.nsub - 1) {   // all sub-accumulators have been read: hand them back to the (leader's) MMA warp
+            if (PAIR && !leader) mbar_arrive_remote(bar_tempty0 + 8u * par, 0u);
+            else mbar_arrive(bar_tempty0 + 8u * par);
+          }
           const int ngroups = (G.BN + 63) / 64;
           for (int g = 0; g < ngroups; ++g)
             tma_store_4d(&G.tm_y, staging + (uint32_t)g * 16384u, n0 + g * 64, w0, h0 + j * G.BH, img);
@@ -207,6 +244,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
       }
     }
     if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem may go once it has been read; the writes complete with the grid
+  }
+  if (PAIR) {
+    // neither CTA may leave (or free TMEM) while the other can still signal its barriers or read its operands
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    cluster_sync_all();
+    if (warp == 1) {
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G.tmem_cols)
+                   : "memory");
+    }
+    return;
   }
   __syncthreads();
   if (warp == 1) {
@@ -284,15 +332,27 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
   A.tiles_w = (W + A.BW - 1) / A.BW;
   A.tiles_h = (H + A.nsub * A.BH - 1) / (A.nsub * A.BH);
   A.tiles_n = (Cout + A.BN - 1) / A.BN;
+  // CTA pairs, by measurement (scripts/pair3_sweep_specs.txt, profiles/round2_pair3_sweep.txt, batch 32): 0.81-0.95x where
+  // the K loop is long (Cin >= 128: the weight tiles are half of a stage's L2 -> SM bytes and the pair halves them),
+  // 1.12-1.21x (slower) for the 64 -> 64 layers, whose three stages per tile do not amortise the cross-CTA handshakes --
+  // the smem-operand bound of N = 64 is NOT what pairs fix.  d.pair / YB_C3_PAIR force (1) or forbid (-1).
+  {
+    static const char* pair_env = getenv("YB_C3_PAIR");
+    int pm = d.pair ? d.pair : (pair_env ? atoi(pair_env) : 0);
+    const long long tiles_all = (long long)A.tiles_w * A.tiles_h * x.N * A.tiles_n;
+    if (pm == 0) pm = (Cin >= 128 && tiles_all >= num_sms()) ? 1 : -1;
+    A.pair = pm > 0 ? 1 : 0;
+  }
+  const int bn_cta = A.pair ? A.BN / 2 : A.BN;
   A.tmem_cols = 4 * A.BN < 32 ? 32 : 4 * A.BN;
-  A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)((A.pair ? 256 : 128) >> 4) << 24);
   A.a_tx = (uint32_t)(A.nsub * A.BH + 2) * A.BW * row_bytes;
   // the last sub-tile's MMA (filter row 2) reads 128 rows from row ((NSUB-1)*BH + 2)*BW: keep those reads inside the stage
   uint32_t need_rows = (uint32_t)(((A.nsub - 1) * A.BH + 2) * A.BW + 128);
   uint32_t slab_rows = (uint32_t)(A.nsub * A.BH + 2) * A.BW;
   if (need_rows > slab_rows) slab_rows = need_rows;
   A.a_bytes = (uint32_t)align_up((size_t)slab_rows * row_bytes, 1024);
-  const size_t stage_bytes = (size_t)A.a_bytes + 3 * (size_t)A.BN * row_bytes;
+  const size_t stage_bytes = (size_t)A.a_bytes + 3 * (size_t)bn_cta * row_bytes;
   const size_t stage_out = (size_t)((A.BN + 63) / 64) * 16384;
   const size_t aux_bytes = 8 * (2 * 12 + 4) + 16 + (size_t)kMaxBias * 4 + 64;
   const size_t budget = 226 * 1024 - 1024 - stage_out - aux_bytes;
@@ -314,7 +374,7 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
   {
     uint64_t dims[3] = {(uint64_t)d.cin_pad, 9, (uint64_t)d.cout_pad};
     uint64_t str[2] = {(uint64_t)d.cin_pad * 2, (uint64_t)d.cin_pad * 2 * 9};
-    uint32_t box[3] = {(uint32_t)A.BK, 1, (uint32_t)A.BN};
+    uint32_t box[3] = {(uint32_t)A.BK, 1, (uint32_t)bn_cta};     // pair mode: each CTA loads half of the N tile
     rc = encode(&A.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, d.weight, dims, str, box, one4, sw_in, "conv3 weights");
     if (rc) { delete P; return rc; }
   }
@@ -327,9 +387,12 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
                 "conv3 output");
     if (rc) { delete P; return rc; }
   }
-  const long long total = (long long)A.tiles_n * A.tiles_w * A.tiles_h * x.N;
-  A.total_tiles = (int)total;
-  P->grid = (int)(total < num_sms() ? total : num_sms());
+  const long long m_total = (long long)A.tiles_w * A.tiles_h * x.N;
+  const long long units = (long long)A.tiles_n * (A.pair ? (m_total + 1) / 2 : m_total);
+  A.total_tiles = (int)units;
+  const int walkers_max = A.pair ? num_sms() / 2 : num_sms();
+  const int walkers = (int)(units < walkers_max ? units : walkers_max);
+  P->grid = A.pair ? 2 * walkers : walkers;
   *out = P;
   return YB_OK;
 }
@@ -337,10 +400,12 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
 int conv3_tc_launch(const Conv3Plan* P, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    YB_CUDA(cudaFuncSetAttribute(k_conv3_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    YB_CUDA(cudaFuncSetAttribute(k_conv3_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    YB_CUDA(cudaFuncSetAttribute(k_conv3_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
-  YB_CUDA(launch_pdl(k_conv3_tc, P->grid, kTcThreads, P->smem, s, P->args));
+  if (P->args.pair) YB_CUDA(launch_pdl_pairs(k_conv3_tc<true>, P->grid, kTcThreads, P->smem, s, P->args));
+  else YB_CUDA(launch_pdl(k_conv3_tc<false>, P->grid, kTcThreads, P->smem, s, P->args));
   return YB_OK;
 }
 
