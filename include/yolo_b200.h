@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define YB_ABI_VERSION 3
+#define YB_ABI_VERSION 4
 
 typedef enum {
   YB_OK = 0,
@@ -80,6 +80,10 @@ typedef struct {
   /* CTA pairs (clusters of two CTAs, tcgen05 cta_group::2: one M = 256 MMA per pair, each CTA loads half of the
    * weight tile): 0 = cost model decides, 1 = force, -1 = never */
   int32_t pair;
+  /* optional second output: MaxPool2d(2, 2) of y (MP, models/common.py:30-36) written by the same kernel from the
+   * tile it has just staged -- the full-resolution tensor is not read again.  data == NULL -> none.  bf16, same
+   * channel count as y, H/2 x W/2 (floor); bf16 1x1 / generic-kernel convs without upsample only. */
+  yb_tensor pool;
 } yb_conv_desc;
 
 int yb_conv2d(const yb_conv_desc* d, void* stream);
@@ -231,6 +235,7 @@ typedef struct {
   int32_t cin_pad, cout_pad;
   int32_t tile_n, stages; /* 0 = auto */
   int32_t pair;           /* yb_conv_desc.pair */
+  int32_t pool_out;       /* YB_OP_CONV: tensor index of the fused 2x2 max-pool output (yb_conv_desc.pool), -1 = none */
 } yb_op;
 
 typedef struct yb_engine yb_engine;

@@ -23,7 +23,7 @@ reps = [eng.profile() for _ in range(5)]
 L = eng.L
 print('op\tkind\tCin\tCout\tk\ts\tHout\tups\tms\tTFLOPs\tGBps_algo')
 tot = 0
-for i, op in enumerate(L.ops):
+for i, op in enumerate(eng.ops):
     ms = sorted(r[i][2] for r in reps)[2]
     tot += ms
     fl = reps[0][i][3]

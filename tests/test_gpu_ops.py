@@ -241,3 +241,39 @@ def test_conv3_slab_cta_pairs(case):
     got = _nchw(y2[..., :Co].float().cpu())
     assert torch.allclose(got, ref, rtol=1.2e-2, atol=1.2e-2), float((got - ref).abs().max())
     assert torch.equal(y1, y2)
+
+
+POOL_CASES = [
+    # (N, H, W, Cin, Cout, k, s, act, tile_n, pair)
+    (2, 40, 40, 64, 64, 1, 1, 1, 0, 0),         # 1x1, one 64-channel group, several tiles per image
+    (1, 80, 80, 128, 256, 1, 1, 1, 0, 0),       # N tile 256: four channel groups per tile
+    (2, 20, 20, 1024, 256, 1, 1, 1, 0, 1),      # CTA pairs + pool
+    (1, 22, 38, 64, 96, 1, 1, 2, 0, 0),         # ragged tiles (W, H not multiples of the tile), Cout 96, LeakyReLU
+    (1, 21, 37, 64, 64, 1, 1, 1, 0, 0),         # odd H and W: floor mode drops the last row / column
+    (2, 40, 40, 64, 128, 3, 1, 1, -1, 0),       # 3x3 through the generic kernel
+    (1, 40, 40, 64, 64, 3, 2, 1, -1, 0),        # stride-2 conv, pooled again
+]
+
+
+@pytest.mark.parametrize('case', POOL_CASES, ids=[str(c) for c in POOL_CASES])
+def test_conv_tc_fused_maxpool(case):
+    """yb_conv_desc.pool: the conv kernel also writes MaxPool2d(2, 2) of its output (MP, models/common.py:30-36) from the
+    staged tile.  The full-resolution output must equal the unfused conv bit for bit, the pooled one the separate pool
+    kernel applied to it (max of the same bf16 values), and both F.max_pool2d of the reference."""
+    from yolo_series_b200 import ops
+    N, H, W, Ci, Co, k, s, act, tn, pair = case
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn((N, Ci, H, W), generator=g).bfloat16().float()
+    w = (torch.randn((Co, Ci, k, k), generator=g) / (Ci * k * k) ** 0.5).bfloat16().float()
+    b = torch.randn((Co,), generator=g)
+    xd = _nhwc(x).cuda().bfloat16()
+    y_plain = ops.conv2d(xd, w, b, s, act, 0.1, 1, tile_n=tn, pair=pair)
+    ho, wo = y_plain.shape[1], y_plain.shape[2]
+    pooled = torch.full((N, ho // 2, wo // 2, y_plain.shape[3]), -7.0, dtype=torch.bfloat16, device='cuda')
+    y = ops.conv2d(xd, w, b, s, act, 0.1, 1, tile_n=tn, pair=pair, pool_out=pooled)
+    torch.cuda.synchronize()
+    assert torch.equal(y, y_plain)
+    want = ops.maxpool2x2(y_plain[..., :Co].contiguous())
+    assert torch.equal(pooled[..., :Co], want)
+    ref = F.max_pool2d(_ref_conv(x, w, b, s, act, 0.1, 1), 2, 2)
+    assert torch.allclose(_nchw(pooled[..., :Co].float().cpu()), ref, rtol=1.2e-2, atol=1.2e-2)

@@ -21,7 +21,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     L = ctypes.CDLL(_lib.LIB_PATH)
     for name in declared:
         assert hasattr(L, name), name
-    assert _lib.lib().yb_abi_version() == 3
+    assert _lib.lib().yb_abi_version() == 4
     assert _lib.lib().yb_nms_workspace_bytes(2, 1000, 85, 0, 0) > 2 * 1000 * 16
 
 

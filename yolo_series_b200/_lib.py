@@ -35,7 +35,7 @@ class ConvDesc(C.Structure):
     _fields_ = [('x', Tensor), ('y', Tensor), ('weight', C.c_void_p), ('bias', C.c_void_p),
                 ('cin_pad', C.c_int32), ('cout_pad', C.c_int32), ('k', C.c_int32), ('stride', C.c_int32),
                 ('act', C.c_int32), ('leaky_slope', C.c_float), ('upsample', C.c_int32), ('res', Tensor),
-                ('tile_n', C.c_int32), ('stages', C.c_int32), ('pair', C.c_int32)]
+                ('tile_n', C.c_int32), ('stages', C.c_int32), ('pair', C.c_int32), ('pool', Tensor)]
 
 
 class HeadLevel(C.Structure):
@@ -47,7 +47,7 @@ class Op(C.Structure):
                 ('out1', C.c_int32), ('out2', C.c_int32), ('k', C.c_int32), ('stride', C.c_int32),
                 ('act', C.c_int32), ('upsample', C.c_int32), ('leaky_slope', C.c_float), ('weight', C.c_int32),
                 ('cin_pad', C.c_int32), ('cout_pad', C.c_int32), ('tile_n', C.c_int32), ('stages', C.c_int32),
-                ('pair', C.c_int32)]
+                ('pair', C.c_int32), ('pool_out', C.c_int32)]
 
 
 class LetterboxSrc(C.Structure):
@@ -140,7 +140,7 @@ def lib():
     L.yb_peer_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
     L.yb_peer_close.argtypes = [C.c_void_p]
     L.yb_peer_free.argtypes = [C.c_void_p]
-    if L.yb_abi_version() != 3:
+    if L.yb_abi_version() != 4:
         raise RuntimeError('libyolo_b200.so ABI version mismatch; rebuild')
     _lib = L
     return L

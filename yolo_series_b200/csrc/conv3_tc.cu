@@ -275,7 +275,7 @@ struct Conv3Plan {
 int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
   const yb_tensor& x = d.x;
   const yb_tensor& y = d.y;
-  if (d.k != 3 || d.stride != 1 || d.upsample != 1 || x.dtype != YB_BF16 || y.dtype != YB_BF16 || d.res.data)
+  if (d.k != 3 || d.stride != 1 || d.upsample != 1 || x.dtype != YB_BF16 || y.dtype != YB_BF16 || d.res.data || d.pool.data)
     return YB_ERR_UNSUPPORTED;
   const int Cin = x.C, Cout = y.C, H = x.H, W = x.W;
   if (Cin < 32 || d.cin_pad < 32) return YB_ERR_UNSUPPORTED;

@@ -40,6 +40,9 @@ struct ConvTcArgs {
   int bias_len;
   int total_tiles;                 // work units: (m, n) tiles, or (pair of m tiles, n) in pair mode
   int pair;                        // 1: CTA pairs (clusters of 2, tcgen05 cta_group::2, M = 256 per MMA)
+  int pool;                        // 1: also write the 2x2 max-pool of every (even-sided, even-origin) output tile
+  __nv_bfloat16* pool_ptr;         // pooled output (N, pool_h, pool_w, .) with pool_cs elements per pixel
+  int pool_h, pool_w, pool_cs, pool_c, tiles_imgs;
   uint32_t idesc;
   unsigned long long* dbg;         // tuning aid (env YB_CONV_TS = device address): globaltimer stamps of CTA 0
 };
@@ -84,6 +87,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   const uint32_t staging = tiles + pipe_bytes;                       // 1024-aligned (all pieces are multiples of 1024)
   const uint32_t round_bytes = (G.out_f32 ? 32768u : 16384u) * (uint32_t)G.epi_cpr;
   const uint32_t staging_bytes = round_bytes * (uint32_t)G.epi_ring;
+  const uint32_t pool_groups = (uint32_t)(G.BN + 63) / 64u;
   unsigned char* aux = tiles_ptr + pipe_bytes + staging_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(aux);  // full[S], empty[S], tmem_full[2], tmem_empty[2], resident
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(aux + 8 * (2 * G.stages + 6));
@@ -314,6 +318,41 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           YB_CTS(7, it == 0);
         }
+        if (G.pool) {
+          // MaxPool2d(2, 2) of the tile just staged (rows = pixels py * BW + px, 128-byte rows, SW128): thread ->
+          // (pooled pixel q, 16-byte chunk j, 64-channel group g) takes the max of its four pixels and stores the 16
+          // bytes straight to global memory (8 lanes = one 128-byte run).  No extra shared memory: the TMA store of
+          // the full tile reads the same staging concurrently, which is fine (both only read); the next tile's writes
+          // to this slot come after the bar.sync at its start.
+          const int tig = alt ? (int)threadIdx.x - 64 - grp * 128 : (int)threadIdx.x - 64;
+          const int half_w = G.BW >> 1;
+          for (int item = tig; item < (int)pool_groups * 256; item += nthr) {
+            const int g = item >> 8, q = (item >> 3) & 31, j = item & 7;
+            const int qy = q / half_w, qx = q - qy * half_w;
+            const int py = (h0 >> 1) + qy, px = (w0 >> 1) + qx, ch = n0 + g * 64 + j * 8;
+            if (py >= G.pool_h || px >= G.pool_w || ch >= G.pool_c || img >= G.tiles_imgs) continue;
+            const uint32_t r00 = (uint32_t)(2 * qy * G.BW + 2 * qx);
+            const uint32_t gb = sbase + (uint32_t)g * 16384u;
+            uint4 v[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const uint32_t r = r00 + (uint32_t)(e & 1) + (uint32_t)(e >> 1) * (uint32_t)G.BW;
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v[e].x), "=r"(v[e].y), "=r"(v[e].z), "=r"(v[e].w)
+                           : "r"(gb + r * 128u + ((((uint32_t)j) ^ (r & 7u)) << 4)));
+            }
+            uint4 o;
+            uint32_t* ow = &o.x;
+            const uint32_t* a0 = &v[0].x; const uint32_t* a1 = &v[1].x; const uint32_t* a2 = &v[2].x; const uint32_t* a3 = &v[3].x;
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+              const __nv_bfloat162 m01 = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(a0 + w), *reinterpret_cast<const __nv_bfloat162*>(a1 + w));
+              const __nv_bfloat162 m23 = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(a2 + w), *reinterpret_cast<const __nv_bfloat162*>(a3 + w));
+              const __nv_bfloat162 m = __hmax2(m01, m23);
+              ow[w] = *reinterpret_cast<const uint32_t*>(&m);
+            }
+            *reinterpret_cast<uint4*>(G.pool_ptr + (((size_t)img * G.pool_h + py) * G.pool_w + px) * G.pool_cs + ch) = o;
+          }
+        }
       }
     };
     if (G.act == YB_ACT_SILU) run(std::integral_constant<int, YB_ACT_SILU>{});
@@ -479,7 +518,15 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   A.sw_mode = A.BK == 64 ? 2 : (A.BK == 32 ? 4 : 6);
   const CUtensorMapSwizzle sw_in = A.BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
                                               : (A.BK == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
-  A.flat = (k == 1 && s == 1 && ups == 1) ? 1 : 0;
+  const bool pool = d.pool.data != nullptr;
+  if (pool) {
+    YB_CHECK_ARG(ups == 1 && y.dtype == YB_BF16 && d.pool.dtype == YB_BF16 && d.pool.C == y.C && d.pool.N == y.N &&
+                     d.pool.H == Ho / 2 && d.pool.W == Wo / 2 && d.pool.c_stride % 8 == 0 && (uintptr_t)d.pool.data % 16 == 0,
+                 "conv(tc): fused max-pool output must be bf16 (N, H/2, W/2, C), 16-byte aligned, without upsample");
+    YB_CHECK_ARG(d.pool.H > 0 && d.pool.W > 0, "conv(tc): fused max-pool needs an output of at least 2 x 2");
+  }
+  A.pool = pool ? 1 : 0;
+  A.flat = (k == 1 && s == 1 && ups == 1 && !pool) ? 1 : 0;
   int images = x.N;
   if (A.flat) {
     const long long M = (long long)x.N * x.H * x.W;
@@ -490,7 +537,8 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
     int best_bw = 1, best_cost = 1 << 30;
     for (int bw = 1; bw <= 128 && bw <= Wo; ++bw) {
       int bh = 128 / bw;
-      if (bh > Ho) bh = Ho;
+      if (pool && ((bw & 1) || (bh & 1) || bw * bh != 128)) continue;   // 2x2 blocks must not straddle tiles
+      if (bh > Ho && !pool) bh = Ho;
       if (bh * sh > 256 || bw * sw > 256) continue;
       int cost = ((Wo + bw - 1) / bw) * ((Ho + bh - 1) / bh);
       if (cost < best_cost || (cost == best_cost && bw > best_bw)) { best_cost = cost; best_bw = bw; }
@@ -498,7 +546,7 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
     static const char* bw_env = getenv("YB_TILE_BW");   // tuning aid
     if (bw_env && atoi(bw_env) > 0 && atoi(bw_env) <= 128) best_bw = atoi(bw_env);
     A.BW = best_bw;
-    A.BH = 128 / best_bw < Ho ? 128 / best_bw : Ho;
+    A.BH = (pool || 128 / best_bw < Ho) ? 128 / best_bw : Ho;
     A.tiles_w = (Wo + A.BW - 1) / A.BW;
     A.tiles_h = (Ho + A.BH - 1) / A.BH;
   }
@@ -605,6 +653,11 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
       if (rc) { delete P; return rc; }
     }
   }
+  if (pool) {
+    A.pool_ptr = (__nv_bfloat16*)d.pool.data; A.pool_h = d.pool.H; A.pool_w = d.pool.W; A.pool_cs = d.pool.c_stride;
+    A.pool_c = (Cout + 7) / 8 * 8 <= d.pool.c_stride ? (Cout + 7) / 8 * 8 : Cout / 8 * 8;   // whole 8-channel chunks
+    A.tiles_imgs = x.N;
+  }
   YB_CHECK_ARG(y.H == Ho * ups && y.W == Wo * ups && y.N == x.N, "conv(tc): output spatial dims mismatch");
   const long long units = (long long)A.tiles_n * (A.pair ? (m_tiles + 1) / 2 : m_tiles);
   YB_CHECK_ARG(units < 0x3fffffffLL, "conv(tc): grid too large");
@@ -645,6 +698,7 @@ extern "C" int yb_conv2d(const yb_conv_desc* d, void* stream) {
   const int Ho = (d->x.H + 2 * pad - d->k) / d->stride + 1, Wo = (d->x.W + 2 * pad - d->k) / d->stride + 1;
   YB_CHECK_ARG(d->y.H == Ho * d->upsample && d->y.W == Wo * d->upsample && d->y.N == d->x.N,
                "yb_conv2d: output dims must be (%d,%d)", Ho * d->upsample, Wo * d->upsample);
+  YB_CHECK_ARG(d->x.dtype != YB_F32 || d->pool.data == nullptr, "yb_conv2d: the fused max-pool output needs the bf16 path");
   if (d->x.dtype == YB_F32) return conv_fp32_launch(*d, (cudaStream_t)stream);
   yb_conv_desc dd = *d;
   if (dd.tile_n >= 0) {   // negative tile_n forces the generic kernel (tests / tuning)

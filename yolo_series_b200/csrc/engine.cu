@@ -109,6 +109,12 @@ extern "C" int yb_engine_create(const yb_tensor* tensors, int n_tensors, const y
     d.weight = e->weights[o.weight]; d.bias = e->biases[o.weight];
     d.cin_pad = o.cin_pad; d.cout_pad = o.cout_pad; d.k = o.k; d.stride = o.stride; d.act = o.act;
     d.leaky_slope = o.leaky_slope; d.upsample = o.upsample; d.tile_n = o.tile_n; d.stages = o.stages; d.pair = o.pair;
+    const bool pooled = o.kind == YB_OP_CONV && o.pool_out >= 0;
+    if (pooled) {
+      if (o.pool_out >= n_tensors) { set_error("yb_engine_create: op %d has an invalid pool_out index", i); yb_engine_destroy(e); return YB_ERR_INVALID; }
+      d.pool = e->tensors[o.pool_out];
+      d.tile_n = d.tile_n > 0 ? -d.tile_n : (d.tile_n == 0 ? -1 : d.tile_n);   // the fused pool lives in the generic kernel
+    }
     int rc = d.tile_n < 0 ? YB_ERR_UNSUPPORTED : conv3_tc_plan_create(d, &e->plans3[i]);
     if (rc == YB_ERR_UNSUPPORTED && d.tile_n >= 0) rc = conv3s2p_plan_create(d, &e->plans_s2p[i]);
     if (rc == YB_ERR_UNSUPPORTED) {

@@ -7,11 +7,12 @@ at yolov7/640/B=32 the whole activation set is 5.5 GB of the 180 GB HBM3e, so a 
 would only add risk.  Weights are packed ``[Cout][kh*kw][Cin_pad]`` in the trunk dtype, bias fp32.
 """
 import ctypes as C
+import os
 
 import torch
 
 from . import _lib
-from ._lib import OP_CONV, OP_STEM, YB_BF16, YB_F32, YB_U8
+from ._lib import OP_CONV, OP_MAXPOOL2, OP_STEM, YB_BF16, YB_F32, YB_U8
 
 
 def _round_up(x, m):
@@ -82,10 +83,26 @@ class Engine:
                 self.views.append(_lib.Tensor(self.img_buf.data_ptr(), _lib.torch_dtype_code(img_dtype), B, H, W,
                                               L.in_ch, L.in_ch))
         self.img_dtype = img_dtype
+        # ---- MP fused into its producer (bf16 path): a 1x1 conv whose output feeds a 2x2 max-pool also writes the
+        # pooled tensor from the tile it has just staged (yb_conv_desc.pool), so the full-resolution tensor is not
+        # re-read by a pool kernel.  Bit-identical to the separate kernel (max of the same bf16 values).
+        self.pool_of = {}            # id(conv op) -> pooled value id
+        skip = set()
+        if dtype == torch.bfloat16 and os.environ.get('YB_NO_POOL_FUSION') is None:
+            producer = {v: op for op in L.ops for v in op.outs}
+            for op in L.ops:
+                if op.kind != OP_MAXPOOL2:
+                    continue
+                src = producer.get(op.ins[0])
+                if (src is not None and src.kind == OP_CONV and src.conv.k == 1 and src.upsample == 1 and src is not stem_op
+                        and not L.vals[op.ins[0]].f32 and id(src) not in self.pool_of):
+                    self.pool_of[id(src)] = op.outs[0]
+                    skip.add(id(op))
+        self.ops = [op for op in L.ops if id(op) not in skip]
         # ---- weights
         self.weights, self.biases, self._keep = [], [], []
-        ops_c = (_lib.Op * len(L.ops))()
-        for i, op in enumerate(L.ops):
+        ops_c = (_lib.Op * len(self.ops))()
+        for i, op in enumerate(self.ops):
             o = ops_c[i]
             o.kind = op.kind
             o.in0 = op.ins[0]
@@ -94,6 +111,7 @@ class Engine:
             o.out1 = op.outs[1] if len(op.outs) > 1 else -1
             o.out2 = op.outs[2] if len(op.outs) > 2 else -1
             o.k, o.stride, o.act, o.upsample, o.leaky_slope, o.weight = op.k, 1, 0, op.upsample, 0.0, -1
+            o.pool_out = self.pool_of.get(id(op), -1)
             if op.kind == OP_CONV:
                 fc = op.conv
                 xin = self.views[op.ins[0]]
@@ -130,10 +148,10 @@ class Engine:
         w_ptrs = (C.c_void_p * max(nw, 1))(*[w.data_ptr() for w in self.weights])
         b_ptrs = (C.c_void_p * max(nw, 1))(*[b.data_ptr() for b in self.biases])
         handle = C.c_void_p()
-        _lib.check(self.lib.yb_engine_create(tens_c, len(self.views), ops_c, len(L.ops), w_ptrs, b_ptrs, nw,
+        _lib.check(self.lib.yb_engine_create(tens_c, len(self.views), ops_c, len(self.ops), w_ptrs, b_ptrs, nw,
                                              C.byref(handle)), 'yb_engine_create')
         self.handle = handle
-        self.n_ops = len(L.ops)
+        self.n_ops = len(self.ops)
         self.head = [self.buffers[v] for v in L.head_vals]        # fp32 NHWC logits per level
         self.head_views = [self.views[v] for v in L.head_vals]
         self.input_view = self.views[L.input_val]
@@ -183,7 +201,7 @@ class Engine:
         with torch.cuda.device(self.device):
             _lib.check(self.lib.yb_engine_profile(self.handle, ms, _lib.stream_ptr()), 'yb_engine_profile')
         rows = []
-        for i, op in enumerate(self.L.ops):
+        for i, op in enumerate(self.ops):
             fl = 0
             if op.kind == OP_CONV:
                 fc = op.conv
@@ -201,11 +219,13 @@ class Engine:
 
     def op_bytes(self, i):
         """Algorithmic HBM bytes of op ``i``: every input and output element once, weights once."""
-        op = self.L.ops[i]
+        op = self.ops[i]
 
         def vb(v, c=None):
             return v.N * v.H * v.W * (v.C if c is None else c) * {YB_F32: 4, YB_BF16: 2, YB_U8: 1}[v.dtype]
         total = sum(vb(self.views[o]) for o in op.outs)
+        if id(op) in self.pool_of:
+            total += vb(self.views[self.pool_of[id(op)]])
         if op.kind == OP_CONV and self.img_buf is not None and self.L.input_val in op.ins:     # fused stem reads the raw image
             total += self.img_buf.numel() * self.img_buf.element_size()
         else:
