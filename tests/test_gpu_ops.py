@@ -277,3 +277,46 @@ def test_conv_tc_fused_maxpool(case):
     assert torch.equal(pooled[..., :Co], want)
     ref = F.max_pool2d(_ref_conv(x, w, b, s, act, 0.1, 1), 2, 2)
     assert torch.allclose(_nchw(pooled[..., :Co].float().cpu()), ref, rtol=1.2e-2, atol=1.2e-2)
+
+
+RES_CASES = [
+    # (N, H, W, Cin, Cout, act, pair, pool)
+    (2, 40, 40, 128, 160, 1, 0, False),      # e6e width 160: five 32-column chunks, flat 1x1
+    (1, 20, 20, 1280, 1280, 1, 1, False),    # CTA pairs, five N tiles of 256
+    (2, 40, 40, 64, 80, 1, 0, True),         # residual + fused max-pool (DownC behind a Shortcut), Cout 80: partial chunk
+    (1, 22, 38, 64, 96, 2, 0, True),         # ragged 2-D tiles, LeakyReLU
+    (3, 9, 13, 32, 64, 0, 0, False),         # odd sizes, no activation
+]
+
+
+@pytest.mark.parametrize('case', RES_CASES, ids=[str(c) for c in RES_CASES])
+def test_conv_tc_fused_residual(case):
+    """yb_conv_desc.res: y = act(conv(x)) + res (Shortcut, models/common.py:80-86) inside the conv epilogue: the sum is
+    formed in fp32 and rounded to bf16 once (the separate add rounds the conv output first), so it is compared with the
+    fp32 reference at the bf16 tolerance and with conv -> yb_add at one bf16 ulp of the larger of |conv| and |sum|; the pooled output must be the max-pool
+    of the fused output bit for bit."""
+    from yolo_series_b200 import ops
+    N, H, W, Ci, Co, act, pair, pool = case
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn((N, Ci, H, W), generator=g).bfloat16().float()
+    w = (torch.randn((Co, Ci, 1, 1), generator=g) / Ci ** 0.5).bfloat16().float()
+    b = torch.randn((Co,), generator=g)
+    r = torch.randn((N, Co, H, W), generator=g).bfloat16().float()
+    ref = _ref_conv(x, w, b, 1, act, 0.1, 1) + r
+    xd, rd = _nhwc(x).cuda().bfloat16(), _nhwc(r).cuda().bfloat16()
+    cb = (Co + 7) // 8 * 8
+    if cb != Co:
+        rd = torch.nn.functional.pad(rd, (0, cb - Co)).contiguous()
+    pooled = torch.zeros((N, H // 2, W // 2, cb), dtype=torch.bfloat16, device='cuda') if pool else None
+    y = ops.conv2d(xd, w, b, 1, act, 0.1, 1, pair=pair, res=rd, pool_out=pooled)
+    torch.cuda.synchronize()
+    got = _nchw(y[..., :Co].float().cpu())
+    assert torch.allclose(got, ref, rtol=1.2e-2, atol=1.2e-2), float((got - ref).abs().max())
+    conv = ops.conv2d(xd, w, b, 1, act, 0.1, 1, pair=pair)[..., :Co].contiguous()
+    y_sep = ops.add(conv, rd[..., :Co].contiguous())
+    d = (y[..., :Co].float() - y_sep.float()).abs()
+    # the separate path rounds the conv output (<= half an ulp of |conv|) and then the sum (<= half an ulp of |sum|)
+    scale = torch.maximum(conv.float().abs(), y_sep.float().abs()).clamp(min=1e-2)
+    assert float((d / scale).max()) <= 2 ** -7
+    if pool:
+        assert torch.equal(pooled[..., :Co], ops.maxpool2x2(y[..., :Co].contiguous()))

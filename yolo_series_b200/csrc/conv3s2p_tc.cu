@@ -213,7 +213,7 @@ struct ConvS2pPlan {
 
 // YB_ERR_UNSUPPORTED = shape not handled here (caller falls back to the generic kernel).
 int conv3s2p_plan_create(const yb_conv_desc& d, ConvS2pPlan** out) {
-  if (d.pool.data) return YB_ERR_UNSUPPORTED;   // the fused max-pool output lives in the generic kernel
+  if (d.pool.data || d.res.data) return YB_ERR_UNSUPPORTED;   // fused max-pool / residual live in the generic kernel
   const yb_tensor& x = d.x;
   const yb_tensor& y = d.y;
   if (d.k != 3 || d.stride != 2 || d.upsample != 1 || x.dtype != YB_BF16 || y.dtype != YB_BF16 || d.res.data)

@@ -43,6 +43,9 @@ struct ConvTcArgs {
   int pool;                        // 1: also write the 2x2 max-pool of every (even-sided, even-origin) output tile
   __nv_bfloat16* pool_ptr;         // pooled output (N, pool_h, pool_w, .) with pool_cs elements per pixel
   int pool_h, pool_w, pool_cs, pool_c, tiles_imgs;
+  const __nv_bfloat16* res_ptr;    // residual added after the activation (NULL = none): (N, out_h, out_w, .) bf16
+  int res_cs, res_c, out_h, out_w; // elements per residual pixel, its channel count rounded up to 8; output extent
+  long long out_pixels;            // N * out_h * out_w (flat mode)
   uint32_t idesc;
   unsigned long long* dbg;         // tuning aid (env YB_CONV_TS = device address): globaltimer stamps of CTA 0
 };
@@ -275,6 +278,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     const uint32_t tile_stage = (G.out_f32 ? 32768u : 16384u) * (uint32_t)G.epi_cpr;
     const uint32_t sbase = staging + (uint32_t)grp * tile_stage;
     const int c_first = alt ? 0 : half, c_step = alt ? 1 : 2;
+    const int r_h = row / G.BW, r_w = row - r_h * G.BW;     // this thread's pixel inside a 2-D tile
     // The activation is a compile-time constant inside the loop (straight-line element code).
     auto run = [&](auto act_c) {
       constexpr int ACT = decltype(act_c)::value;
@@ -295,8 +299,32 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
         if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(nthr) : "memory");
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * (uint32_t)G.BN;
+        // residual: this thread's pixel of the other branch (flat mode: pixel index; 2-D tiles: row / BW, row % BW)
+        const __nv_bfloat16* rpix = nullptr;
+        if (G.res_ptr) {
+          if (G.flat) {
+            const long long pix = (long long)w0 + row;
+            if (img == 0 && pix < G.out_pixels) rpix = G.res_ptr + pix * G.res_cs;
+          } else {
+            const int hh = h0 + r_h, ww = w0 + r_w;
+            if (img < G.tiles_imgs && hh < G.out_h && ww < G.out_w)
+              rpix = G.res_ptr + (((long long)img * G.out_h + hh) * G.out_w + ww) * G.res_cs;
+          }
+        }
         for (int cc = c_first; cc < nchunks; cc += c_step) {
           uint32_t v[32];
+          if (G.res_ptr) {   // loads issued before the TMEM wait so that their latency overlaps it
+            uint4 res[4];
+            const int ch0 = n0 + cc * 32;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              res[j] = (rpix && ch0 + 8 * j < G.res_c) ? __ldg(reinterpret_cast<const uint4*>(rpix + ch0 + 8 * j))
+                                                       : make_uint4(0u, 0u, 0u, 0u);
+            tmem_ld32(taddr + (uint32_t)(cc * 32), v);
+            epi_chunk_bf16_res<ACT>(v, bias_s + ch0, G.slope, res, sbase + (uint32_t)(cc >> 1) * 16384u + (uint32_t)row * 128u,
+                                    (uint32_t)(cc & 1), xr);
+            continue;
+          }
           tmem_ld32(taddr + (uint32_t)(cc * 32), v);
           const float* bs = bias_s + n0 + cc * 32;
           if (G.out_f32) epi_chunk_f32<ACT>(v, bs, G.slope, sbase + (uint32_t)cc * 16384u + (uint32_t)row * 128u, xr);
@@ -479,7 +507,6 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   const yb_tensor& y = d.y;
   YB_CHECK_ARG(x.dtype == YB_BF16, "conv(tc): x must be bf16");
   YB_CHECK_ARG(y.dtype == YB_BF16 || y.dtype == YB_F32, "conv(tc): y must be bf16 or fp32");
-  YB_CHECK_ARG(d.res.data == nullptr, "conv(tc): fused residual not supported; use yb_add");
   YB_CHECK_ARG(x.c_stride % 8 == 0 && d.cin_pad % 8 == 0 && (uintptr_t)x.data % 16 == 0 && (uintptr_t)d.weight % 16 == 0,
                "conv(tc): input channel stride / cin_pad must be multiples of 8 and pointers 16-byte aligned");
   const int y_es = y.dtype == YB_F32 ? 4 : 2;
@@ -525,6 +552,14 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
                  "conv(tc): fused max-pool output must be bf16 (N, H/2, W/2, C), 16-byte aligned, without upsample");
     YB_CHECK_ARG(d.pool.H > 0 && d.pool.W > 0, "conv(tc): fused max-pool needs an output of at least 2 x 2");
   }
+  if (d.res.data) {
+    YB_CHECK_ARG(ups == 1 && y.dtype == YB_BF16 && d.res.dtype == YB_BF16 && d.res.N == y.N && d.res.H == Ho && d.res.W == Wo &&
+                     d.res.C == y.C && d.res.c_stride % 8 == 0 && (uintptr_t)d.res.data % 16 == 0,
+                 "conv(tc): residual must be a bf16 (N, Ho, Wo, Cout) tensor, 16-byte aligned, without upsample");
+    A.res_ptr = (const __nv_bfloat16*)d.res.data; A.res_cs = d.res.c_stride;
+    A.res_c = (Cout + 7) / 8 * 8 <= d.res.c_stride ? (Cout + 7) / 8 * 8 : Cout / 8 * 8;
+  }
+  A.out_h = Ho; A.out_w = Wo; A.out_pixels = (long long)x.N * Ho * Wo; A.tiles_imgs = x.N;
   A.pool = pool ? 1 : 0;
   A.flat = (k == 1 && s == 1 && ups == 1 && !pool) ? 1 : 0;
   int images = x.N;
@@ -698,7 +733,8 @@ extern "C" int yb_conv2d(const yb_conv_desc* d, void* stream) {
   const int Ho = (d->x.H + 2 * pad - d->k) / d->stride + 1, Wo = (d->x.W + 2 * pad - d->k) / d->stride + 1;
   YB_CHECK_ARG(d->y.H == Ho * d->upsample && d->y.W == Wo * d->upsample && d->y.N == d->x.N,
                "yb_conv2d: output dims must be (%d,%d)", Ho * d->upsample, Wo * d->upsample);
-  YB_CHECK_ARG(d->x.dtype != YB_F32 || d->pool.data == nullptr, "yb_conv2d: the fused max-pool output needs the bf16 path");
+  YB_CHECK_ARG(d->x.dtype != YB_F32 || (d->pool.data == nullptr && d->res.data == nullptr),
+               "yb_conv2d: the fused max-pool output / residual need the bf16 path");
   if (d->x.dtype == YB_F32) return conv_fp32_launch(*d, (cudaStream_t)stream);
   yb_conv_desc dd = *d;
   if (dd.tile_n >= 0) {   // negative tile_n forces the generic kernel (tests / tuning)

@@ -109,6 +109,10 @@ extern "C" int yb_engine_create(const yb_tensor* tensors, int n_tensors, const y
     d.weight = e->weights[o.weight]; d.bias = e->biases[o.weight];
     d.cin_pad = o.cin_pad; d.cout_pad = o.cout_pad; d.k = o.k; d.stride = o.stride; d.act = o.act;
     d.leaky_slope = o.leaky_slope; d.upsample = o.upsample; d.tile_n = o.tile_n; d.stages = o.stages; d.pair = o.pair;
+    if (o.kind == YB_OP_CONV && o.in1 >= 0) {   // residual: y = act(conv(in0)) + in1 (a Shortcut folded into its producer)
+      d.res = e->tensors[o.in1];
+      d.tile_n = d.tile_n > 0 ? -d.tile_n : (d.tile_n == 0 ? -1 : d.tile_n);
+    }
     const bool pooled = o.kind == YB_OP_CONV && o.pool_out >= 0;
     if (pooled) {
       if (o.pool_out >= n_tensors) { set_error("yb_engine_create: op %d has an invalid pool_out index", i); yb_engine_destroy(e); return YB_ERR_INVALID; }

@@ -147,6 +147,28 @@ __device__ __forceinline__ void epi_chunk_bf16(const uint32_t (&v)[32], const fl
                  : "memory");
   }
 }
+// Same with a residual (Shortcut, models/common.py:85-86: y = act(conv) + res): `res` holds this pixel's 32 bf16 values of
+// the other branch (zeros where it has none); the sum is formed in fp32 and rounded to bf16 once.
+template <int ACT>
+__device__ __forceinline__ void epi_chunk_bf16_res(const uint32_t (&v)[32], const float* bs, float slope, const uint4 (&res)[4],
+                                                   uint32_t row_base, uint32_t sub, uint32_t xr) {
+  float f[32];
+  epi_bias_act<ACT>(v, bs, slope, f);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t rw[4] = {res[j].x, res[j].y, res[j].z, res[j].w};
+    uint32_t p[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const __nv_bfloat162 r2 = *reinterpret_cast<const __nv_bfloat162*>(&rw[e]);
+      __nv_bfloat162 hh = __floats2bfloat162_rn(f[8 * j + 2 * e] + __low2float(r2), f[8 * j + 2 * e + 1] + __high2float(r2));
+      p[e] = *reinterpret_cast<uint32_t*>(&hh);
+    }
+    const uint32_t addr = row_base + (((sub * 4u + (uint32_t)j) ^ xr) << 4);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(p[0]), "r"(p[1]), "r"(p[2]), "r"(p[3])
+                 : "memory");
+  }
+}
 // fp32 output: the chunk is a whole 128-byte staging row (32 channels).
 template <int ACT>
 __device__ __forceinline__ void epi_chunk_f32(const uint32_t (&v)[32], const float* bs, float slope, uint32_t row_base,

@@ -12,7 +12,7 @@ import os
 import torch
 
 from . import _lib
-from ._lib import OP_CONV, OP_MAXPOOL2, OP_STEM, YB_BF16, YB_F32, YB_U8
+from ._lib import OP_ADD, OP_CONV, OP_MAXPOOL2, OP_STEM, YB_BF16, YB_F32, YB_U8
 
 
 def _round_up(x, m):
@@ -47,8 +47,9 @@ class Engine:
                 v = L.vals[v].parent
             return v, off
 
-        used = set()
-        for op in L.ops:
+        self.ops, self.pool_of = self._fuse_elementwise(L, dtype)
+        used = set(self.pool_of.values())
+        for op in self.ops:
             used.update(op.ins)
             used.update(op.outs)
         used.add(L.input_val)
@@ -74,7 +75,7 @@ class Engine:
         # ---- fused staging + first conv (bf16 path): the stem kernel reads the raw NCHW image itself
         self.img_buf, stem_op = None, None
         if dtype == torch.bfloat16 and fuse_stem:
-            readers = [op for op in L.ops if L.input_val in op.ins]
+            readers = [op for op in self.ops if L.input_val in op.ins]
             if (len(readers) == 1 and readers[0].kind == OP_CONV and readers[0].conv.k == 3 and readers[0].upsample == 1
                     and readers[0].conv.c_in <= 16 and readers[0].conv.c_out % 16 == 0 and readers[0].conv.c_out <= 96
                     and not L.vals[readers[0].outs[0]].f32):
@@ -83,22 +84,6 @@ class Engine:
                 self.views.append(_lib.Tensor(self.img_buf.data_ptr(), _lib.torch_dtype_code(img_dtype), B, H, W,
                                               L.in_ch, L.in_ch))
         self.img_dtype = img_dtype
-        # ---- MP fused into its producer (bf16 path): a 1x1 conv whose output feeds a 2x2 max-pool also writes the
-        # pooled tensor from the tile it has just staged (yb_conv_desc.pool), so the full-resolution tensor is not
-        # re-read by a pool kernel.  Bit-identical to the separate kernel (max of the same bf16 values).
-        self.pool_of = {}            # id(conv op) -> pooled value id
-        skip = set()
-        if dtype == torch.bfloat16 and os.environ.get('YB_NO_POOL_FUSION') is None:
-            producer = {v: op for op in L.ops for v in op.outs}
-            for op in L.ops:
-                if op.kind != OP_MAXPOOL2:
-                    continue
-                src = producer.get(op.ins[0])
-                if (src is not None and src.kind == OP_CONV and src.conv.k == 1 and src.upsample == 1 and src is not stem_op
-                        and not L.vals[op.ins[0]].f32 and id(src) not in self.pool_of):
-                    self.pool_of[id(src)] = op.outs[0]
-                    skip.add(id(op))
-        self.ops = [op for op in L.ops if id(op) not in skip]
         # ---- weights
         self.weights, self.biases, self._keep = [], [], []
         ops_c = (_lib.Op * len(self.ops))()
@@ -106,7 +91,7 @@ class Engine:
             o = ops_c[i]
             o.kind = op.kind
             o.in0 = op.ins[0]
-            o.in1 = op.ins[1] if len(op.ins) > 1 else -1
+            o.in1 = op.ins[1] if len(op.ins) > 1 else -1     # OP_ADD: second term; OP_CONV: residual (fused Shortcut)
             o.out0 = op.outs[0]
             o.out1 = op.outs[1] if len(op.outs) > 1 else -1
             o.out2 = op.outs[2] if len(op.outs) > 2 else -1
@@ -156,6 +141,63 @@ class Engine:
         self.head_views = [self.views[v] for v in L.head_vals]
         self.input_view = self.views[L.input_val]
         self.conv_flops = self._count_flops()
+
+    @staticmethod
+    def _fuse_elementwise(L, dtype):
+        """bf16 path: fold the element-wise neighbours of 1x1 convs into the conv kernel's epilogue.  Returns
+        (ops, pool_of): the op list to run (copies where an op was changed -- the lowered graph is shared between
+        engines) and {id(conv op): pooled value id}.
+
+        * Shortcut (OP_ADD, models/common.py:80-86): ``a + b`` where the later-computed term is the output of a 1x1 conv
+          that nobody else reads -> that conv adds the other term as a residual after its activation and writes the
+          sum (yb_conv_desc.res); the add kernel and one round trip of the tensor disappear.
+        * MP (OP_MAXPOOL2, common.py:30-36) whose input comes from a 1x1 conv -> the conv also writes the 2x2 max-pool
+          of every tile it has staged (yb_conv_desc.pool); bit-identical to the separate pool kernel.
+        """
+        import dataclasses
+        ops = list(L.ops)
+        pool_of = {}
+        if dtype != torch.bfloat16 or os.environ.get('YB_NO_EPILOGUE_FUSION') is not None:
+            return ops, pool_of
+
+        def fusable_conv(op):
+            return (op is not None and op.kind == OP_CONV and op.conv.k == 1 and op.upsample == 1 and len(op.ins) == 1
+                    and L.input_val not in op.ins and not L.vals[op.outs[0]].f32)
+        if os.environ.get('YB_NO_RES_FUSION') is None:
+            pos = {id(op): i for i, op in enumerate(ops)}
+            producer = {v: op for op in ops for v in op.outs}
+            readers = {}                     # live readers per value (Val.users still counts ops dropped as dead code)
+            for op in ops:
+                for v in op.ins:
+                    readers[v] = readers.get(v, 0) + 1
+            for v in list(L.head_vals) + list(L.aux_vals):
+                readers[v] = readers.get(v, 0) + 1
+            for add in [o for o in ops if o.kind == OP_ADD]:
+                a, b = add.ins[0], add.ins[1]
+                pa, pb = producer.get(a), producer.get(b)
+                if pa is None or pb is None:
+                    continue
+                # the term computed LAST carries the add; the other one is ready by then
+                (late, lv), (early_v) = ((pa, a), b) if pos[id(pa)] > pos[id(pb)] else ((pb, b), a)
+                v = L.vals[lv]
+                if not fusable_conv(late) or readers.get(lv, 0) != 1 or v.parent is not None or v.is_concat:
+                    continue
+                fused = dataclasses.replace(late, ins=[late.ins[0], early_v], outs=list(add.outs), name=late.name + '+add')
+                i = pos[id(late)]
+                ops[i] = fused
+                ops.remove(add)
+                pos = {id(op): k for k, op in enumerate(ops)}
+                producer = {vv: op for op in ops for vv in op.outs}
+        if os.environ.get('YB_NO_POOL_FUSION') is None:
+            producer = {v: op for op in ops for v in op.outs}
+            for mp in [o for o in ops if o.kind == OP_MAXPOOL2]:
+                src = producer.get(mp.ins[0])
+                if fusable_conv(src) or (src is not None and src.kind == OP_CONV and src.conv.k == 1 and src.upsample == 1
+                                         and len(src.ins) == 2 and not L.vals[src.outs[0]].f32):
+                    if id(src) not in pool_of:
+                        pool_of[id(src)] = mp.outs[0]
+                        ops.remove(mp)
+        return ops, pool_of
 
     def _count_flops(self):
         total = 0

@@ -17,7 +17,7 @@ def pack_weight(w, cin_pad, dtype):
 
 
 def conv2d(x, w, b, stride=1, act=ACT_NONE, slope=0.0, upsample=1, out=None, out_c_off=0, out_dtype=None,
-           tile_n=0, stages=0, pair=0, pool_out=None):
+           tile_n=0, stages=0, pair=0, pool_out=None, res=None):
     """x: (N,H,W,Cx) NHWC cuda tensor (bf16 -> tcgen05 path, fp32 -> reference-mode path);
     w: (Cout, Cin, k, k) fp32 with Cin <= Cx; b: (Cout,) fp32."""
     L = _lib.lib()
@@ -39,6 +39,8 @@ def conv2d(x, w, b, stride=1, act=ACT_NONE, slope=0.0, upsample=1, out=None, out
     d.cin_pad, d.cout_pad, d.k, d.stride = cin_pad, co, k, stride
     d.act, d.leaky_slope, d.upsample = act, slope, upsample
     d.tile_n, d.stages, d.pair = tile_n, stages, pair
+    if res is not None:           # y = act(conv) + res (Shortcut folded into the conv)
+        d.res = _lib.view(res, 0, co)
     if pool_out is not None:      # fused MaxPool2d(2, 2) of the output (second tensor written by the same kernel)
         d.pool = _lib.view(pool_out, 0, co)
     _lib.check(L.yb_conv2d(C.byref(d), _lib.stream_ptr()), 'yb_conv2d')
