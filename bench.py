@@ -94,7 +94,7 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
         t0, t1 = getattr(self, 't0', 0.0), getattr(self, 't1', float('inf'))
         inside = [r[1:] for r in self.rows if t0 <= r[0] <= t1 + 0.12]
@@ -105,11 +105,15 @@ class ClockSampler:
                 sm.append(float(r[0])); mx.append(float(r[1]))
             except ValueError:
                 continue
+            try:
+                pw.append(float(r[2]))
+            except ValueError:
+                pass
             for n, v in zip(names, r[3:7]):
                 if v.lower().startswith('active'):
                     reasons.add(n)
         return {'sm_mhz': statistics.median(sm) if sm else None, 'sm_max_mhz': max(mx) if mx else None,
-                'samples': len(sm), 'reasons': sorted(reasons)}
+                'power_w': statistics.median(pw) if pw else None, 'samples': len(sm), 'reasons': sorted(reasons)}
 
 
 def cpu_reference_step(cfg, sd, imgs, threads):

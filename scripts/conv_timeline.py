@@ -12,7 +12,7 @@ from yolo_series_b200 import _lib, ops  # noqa: E402
 NAMES = ['entry', 'setup done', 'pdl_wait done', 'first TMA issued', 'first operands landed', 'last MMA committed',
          'accumulator ready', 'TMA store issued', 'store smem read', 'exit']
 L = _lib.lib()
-ts = torch.zeros(16, dtype=torch.int64, device='cuda')
+ts = torch.zeros(16 * 1024, dtype=torch.int64, device='cuda')      # 16 stamps per CTA; CTA 0 is printed
 os.environ['YB_CONV_TS'] = hex(ts.data_ptr())
 for spec in sys.argv[1:]:
     ci, co, k, s, h, B = [int(t) for t in spec.split(',')]

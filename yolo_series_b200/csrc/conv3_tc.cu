@@ -23,6 +23,7 @@ struct Conv3Args {
   CUtensorMap tm_y;
   const float* bias;
   int tiles_n, tiles_w, tiles_h;   // super-tile grid per image
+  FastDiv fd_n, fd_mimg, fd_w;     // divisions by tiles_n, tiles_w * tiles_h, tiles_w (tc_common.cuh)
   int BW, BH, BN, BK;
   int nsub;                        // sub-tiles per CTA tile: 2 (super-tile, weights shared) or 1 (grids short of CTAs)
   int kchunks, stages;
@@ -64,6 +65,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
   const bool leader = rank == 0u;
+  if (warp == 2) warm_param_lines(G);     // tc_common.cuh: parameter lines are cold per launch
   const uint32_t bn_cta = PAIR ? (uint32_t)G.BN / 2u : (uint32_t)G.BN;
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
@@ -102,7 +104,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
   }
   {   // bias of the channels this launch can touch (the last N tile may reach past Cout: zeros there)
     const int nb = min(kMaxBias, (G.bias_len + 255) & ~255);
-    for (int i = threadIdx.x; i < nb; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
+    const float bsc = epi_bias_scale(G.act);
+    for (int i = threadIdx.x; i < nb; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? bsc * G.bias[i] : 0.f;
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   if (PAIR) cluster_sync_all();     // the peer's barriers must exist before anything signals them
@@ -112,7 +115,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
   const int walker = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int walkers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   pdl_launch_dependents();   // set-up done: the next kernel's CTAs may take SMs as ours retire
-  pdl_wait();                // activations written by the previous kernel are visible from here on
+  // griddepcontrol.wait: the producer warp alone, after the arithmetic of its first tile (see k_conv_tc)
   const int tiles_m_per_img = G.tiles_w * G.tiles_h;
   const int stages_per_tile = 3 * G.kchunks;
 
@@ -121,14 +124,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
     // Warp-uniform control flow, one elected lane issues the copies (coordinates live in uniform registers).
     const uint32_t tx = (PAIR ? 2u : 1u) * (G.a_tx + 3u * b_bytes);   // the leader's barrier collects both CTAs' bytes
     uint32_t s = 0, ph = 1;  // ring slot + parity to wait for on its empty barrier
+    bool first = true;
     for (int t = walker; t < G.total_tiles; t += walkers) {
-      const int n_tile = t % G.tiles_n;
-      int m_tile = t / G.tiles_n;
-      if (PAIR) m_tile = 2 * m_tile + (int)rank;   // a tile past the end loads zeros and stores nothing (TMA clips)
-      const int img = m_tile / tiles_m_per_img;
+      const int t_m = fd_div(t, G.fd_n);
+      const int n_tile = t - t_m * G.tiles_n;
+      int m_tile = PAIR ? 2 * t_m + (int)rank : t_m;   // a tile past the end loads zeros and stores nothing (TMA clips)
+      const int img = fd_div(m_tile, G.fd_mimg);
       m_tile -= img * tiles_m_per_img;
-      const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+      const int th = fd_div(m_tile, G.fd_w), tw = m_tile - th * G.tiles_w;
       const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.nsub * G.BH;
+      if (first) {
+        asm volatile("" ::"r"(n0), "r"(w0), "r"(h0), "r"(img));     // coordinates first, then the wait
+        pdl_wait();                // activations written by the previous kernel are visible from here on
+        first = false;
+      }
       for (int kk = 0; kk < G.kchunks; ++kk) {
 #pragma unroll
         for (int dx = 0; dx < 3; ++dx) {
@@ -214,12 +223,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
     int it = 0;
     for (int t = walker; t < G.total_tiles; t += walkers, ++it) {
       const uint32_t par = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
-      const int n_tile = t % G.tiles_n;
-      int m_tile = t / G.tiles_n;
-      if (PAIR) m_tile = 2 * m_tile + (int)rank;   // a tile past the end loads zeros and stores nothing (TMA clips)
-      const int img = m_tile / tiles_m_per_img;
+      const int t_m = fd_div(t, G.fd_n);
+      const int n_tile = t - t_m * G.tiles_n;
+      int m_tile = PAIR ? 2 * t_m + (int)rank : t_m;   // a tile past the end loads zeros and stores nothing (TMA clips)
+      const int img = fd_div(m_tile, G.fd_mimg);
       m_tile -= img * tiles_m_per_img;
-      const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+      const int th = fd_div(m_tile, G.fd_w), tw = m_tile - th * G.tiles_w;
       const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.nsub * G.BH;
       mbar_wait(bar_tfull0 + 8u * par, aph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -332,6 +341,7 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
   A.tiles_w = (W + A.BW - 1) / A.BW;
   A.tiles_h = (H + A.nsub * A.BH - 1) / (A.nsub * A.BH);
   A.tiles_n = (Cout + A.BN - 1) / A.BN;
+  A.fd_n = make_fastdiv(A.tiles_n); A.fd_mimg = make_fastdiv(A.tiles_w * A.tiles_h); A.fd_w = make_fastdiv(A.tiles_w);
   // CTA pairs, by measurement (scripts/pair3_sweep_specs.txt, profiles/round2_pair3_sweep.txt, batch 32): 0.81-0.95x where
   // the K loop is long (Cin >= 128: the weight tiles are half of a stage's L2 -> SM bytes and the pair halves them),
   // 1.12-1.21x (slower) for the 64 -> 64 layers, whose three stages per tile do not amortise the cross-CTA handshakes --

@@ -39,6 +39,7 @@ struct ConvS2pArgs {
 __global__ void __launch_bounds__(kTcThreads, 1) k_conv3s2p_tc(const __grid_constant__ ConvS2pArgs G) {
   extern __shared__ unsigned char smem_dyn[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 2) warm_param_lines(G);     // tc_common.cuh: parameter lines are cold per launch
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
   unsigned char* tiles_ptr = smem_dyn + (tiles - raw);
@@ -73,7 +74,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3s2p_tc(const __grid_cons
   }
   {   // bias of the channels this launch can touch (the last N tile may reach past Cout: zeros there)
     const int nb = min(kMaxBias, (G.bias_len + 255) & ~255);
-    for (int i = threadIdx.x; i < nb; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
+    const float bsc = epi_bias_scale(G.act);
+    for (int i = threadIdx.x; i < nb; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? bsc * G.bias[i] : 0.f;
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();

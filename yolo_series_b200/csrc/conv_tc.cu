@@ -25,6 +25,7 @@ struct ConvTcArgs {
   CUtensorMap tm_y[4];
   const float* bias;
   int tiles_n, tiles_w, tiles_h;   // tile grid; m tiles = tiles_w * tiles_h * images
+  FastDiv fd_n, fd_mimg, fd_w;     // divisions by tiles_n, tiles_w * tiles_h, tiles_w
   int BW, BH, BN, BK;              // spatial box, N tile, K chunk (channels)
   int taps, kw, stride_h, stride_w, pad_h, pad_w;   // taps = kh * kw, tap = dy * kw + dx
   int epi_ring, epi_cpr;           // output staging ring (in rounds) and 32-column chunks per warp per round
@@ -47,16 +48,17 @@ struct ConvTcArgs {
   int res_cs, res_c, out_h, out_w; // elements per residual pixel, its channel count rounded up to 8; output extent
   long long out_pixels;            // N * out_h * out_w (flat mode)
   uint32_t idesc;
-  unsigned long long* dbg;         // tuning aid (env YB_CONV_TS = device address): globaltimer stamps of CTA 0
+  unsigned long long* dbg;         // tuning aid (env YB_CONV_TS = device address): globaltimer stamps, 16 per CTA
 };
 
-// stamp `slot` from one thread of CTA 0 when the debug buffer is set (scripts/conv_timeline.py)
+// stamp `slot` of this CTA's 16-entry row from one thread when the debug buffer is set (scripts/conv_timeline.py,
+// scripts/conv_chain_timeline.py; the buffer holds 16 x grid entries)
 #define YB_CTS(slot, cond)                                                                                  \
   do {                                                                                                      \
-    if (G.dbg && blockIdx.x == 0 && (cond)) {                                                               \
+    if (G.dbg && (cond)) {                                                                                  \
       unsigned long long t_;                                                                                \
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                \
-      G.dbg[slot] = t_;                                                                                     \
+      G.dbg[blockIdx.x * 16 + slot] = t_;                                                                   \
     }                                                                                                       \
   } while (0)
 
@@ -76,6 +78,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
   const bool leader = rank == 0u;
   YB_CTS(0, threadIdx.x == 0);
+  if (warp == 2) warm_param_lines(G);
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
   unsigned char* tiles_ptr = smem_dyn + (tiles - raw);
@@ -122,7 +125,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   }
   {   // bias of the channels this launch can touch (the last N tile may reach past Cout: zeros there)
     const int nb = min(kMaxBias, (G.bias_len + 255) & ~255);
-    for (int i = threadIdx.x; i < nb; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? G.bias[i] : 0.f;
+    const float bsc = epi_bias_scale(G.act);
+    for (int i = threadIdx.x; i < nb; i += kTcThreads) bias_s[i] = (i < G.bias_len) ? bsc * G.bias[i] : 0.f;
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   if (PAIR) cluster_sync_all();     // the peer's barriers must exist before anything signals them
@@ -157,8 +161,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
   }
   YB_CTS(1, threadIdx.x == 0);
   pdl_launch_dependents();   // set-up done: the next kernel's CTAs may take SMs as ours retire
-  pdl_wait();                // activations written by the previous kernel are visible from here on
-  YB_CTS(2, threadIdx.x == 0);
+  // griddepcontrol.wait is taken by the producer warp only, AFTER it has worked out its first tile (that arithmetic
+  // then overlaps the previous kernel's tail instead of following it); everything the other warps touch that an
+  // earlier kernel wrote or still reads -- accumulators, the output, the residual -- is ordered behind the
+  // producer's loads through the mbarrier chain (the epilogue takes the wait itself before residual loads).
 
   if (warp == 0) {
     // ================================ TMA producer ================================
@@ -166,19 +172,26 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     const uint32_t tx1 = (uint32_t)(G.BW * G.BH) * G.BK * 2u + (G.resident ? 0u : b_bytes);
     const uint32_t tx = PAIR ? 2u * tx1 : tx1;      // the leader's barrier collects the bytes of both CTAs
     uint32_t s = 0, ph = 1;  // ring slot + parity to wait for on its empty barrier
+    bool first = true;
     for (int t = t_first; t < t_end; t += t_step) {
-      const int n_tile = G.resident ? res_n : t % G.tiles_n;
-      int m_tile = G.resident ? t : t / G.tiles_n;
-      if (PAIR) m_tile = 2 * m_tile + (int)rank;
-      const int img = m_tile / tiles_m_per_img;
+      const int t_m = G.resident ? t : fd_div(t, G.fd_n);
+      const int n_tile = G.resident ? res_n : t - t_m * G.tiles_n;
+      int m_tile = PAIR ? 2 * t_m + (int)rank : t_m;
+      const int img = fd_div(m_tile, G.fd_mimg);
       m_tile -= img * tiles_m_per_img;
-      const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+      const int th = fd_div(m_tile, G.fd_w), tw = m_tile - th * G.tiles_w;
       const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
       int dy = 0, dx = 0;
       for (int tap = 0; tap < G.taps; ++tap) {
         const int cw = w0 * G.stride_w + dx - G.pad_w;
         const int chh = G.flat ? 0 : h0 * G.stride_h + dy - G.pad_h;
         for (int kk = 0; kk < G.kchunks; ++kk) {
+          if (first) {
+            asm volatile("" ::"r"(cw), "r"(chh), "r"(img), "r"(n0));     // coordinates first, then the wait
+            pdl_wait();                 // activations written by the previous kernel are visible from here on
+            YB_CTS(2, lane == 0);
+            first = false;
+          }
           mbar_wait(bar_empty0 + 8u * s, ph);
           if (elect_one()) {
             const uint32_t full = bar_full0 + 8u * s;
@@ -279,18 +292,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     const uint32_t sbase = staging + (uint32_t)grp * tile_stage;
     const int c_first = alt ? 0 : half, c_step = alt ? 1 : 2;
     const int r_h = row / G.BW, r_w = row - r_h * G.BW;     // this thread's pixel inside a 2-D tile
+    if (G.res_ptr) pdl_wait();     // the residual is read with plain loads, ahead of the accumulator barrier
     // The activation is a compile-time constant inside the loop (straight-line element code).
     auto run = [&](auto act_c) {
       constexpr int ACT = decltype(act_c)::value;
       int it = grp;
       for (int t = t_first + grp * t_step; t < t_end; t += (alt ? 2 : 1) * t_step, it += alt ? 2 : 1) {
         const uint32_t acc = (uint32_t)it & 1u, aph = ((uint32_t)it >> 1) & 1u;
-        const int n_tile = G.resident ? res_n : t % G.tiles_n;
-        int m_tile = G.resident ? t : t / G.tiles_n;
-        if (PAIR) m_tile = 2 * m_tile + (int)rank;
-        const int img = m_tile / tiles_m_per_img;
+        const int t_m = G.resident ? t : fd_div(t, G.fd_n);
+        const int n_tile = G.resident ? res_n : t - t_m * G.tiles_n;
+        int m_tile = PAIR ? 2 * t_m + (int)rank : t_m;
+        const int img = fd_div(m_tile, G.fd_mimg);
         m_tile -= img * tiles_m_per_img;
-        const int th = m_tile / G.tiles_w, tw = m_tile - th * G.tiles_w;
+        const int th = fd_div(m_tile, G.fd_w), tw = m_tile - th * G.tiles_w;
         const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.BH;
         mbar_wait(bar_tfull0 + 8u * acc, aph);
         YB_CTS(6, store_thread && it == 0);
@@ -600,6 +614,8 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   YB_CHECK_ARG(A.BN == 32 || A.BN == 64 || A.BN == 128 || A.BN == 256, "conv(tc): tile_n must be 32/64/128/256");
   const int bn_cta = A.pair ? A.BN / 2 : A.BN;
   A.tiles_n = (Cout + A.BN - 1) / A.BN;
+  YB_CHECK_ARG(m_tiles < 0x3fffffffLL, "conv(tc): grid too large");
+  A.fd_n = make_fastdiv(A.tiles_n); A.fd_mimg = make_fastdiv(A.tiles_w * A.tiles_h); A.fd_w = make_fastdiv(A.tiles_w);
   A.n_store_maps = ups == 2 ? 4 : 1;
   A.tmem_cols = 2 * A.BN < 32 ? 32 : 2 * A.BN;   // double-buffered accumulators (64/128/256/512 columns)
   A.idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(A.BN >> 3) << 17) | ((uint32_t)((A.pair ? 256 : 128) >> 4) << 24);

@@ -40,6 +40,42 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
                ::"l"(tm), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
+// Division of a tile index by a launch constant: n / d = (n * mul) >> shift for 0 <= n <= 2^30 with mul = ceil(2^k / d),
+// k = 31 + floor(log2 d) (the error term n * (mul * d - 2^k) stays below 2^k).  A runtime 32-bit division is ~30
+// dependent instructions; the role warps decompose a tile index with three or four of them per tile, which a lone warp
+// executes in about a microsecond (scripts/conv_chain_timeline.py) -- on the critical path of the first tile of every
+// launch and of the same order as a short-K tile's period.
+struct FastDiv {
+  uint32_t mul, shift;
+};
+inline FastDiv make_fastdiv(int d) {
+  FastDiv f;
+  int l = 0;
+  while ((2ll << l) <= (long long)d) ++l;
+  const int k = 31 + l;
+  f.mul = (uint32_t)(((1ull << k) + (unsigned long long)d - 1ull) / (unsigned long long)d);
+  f.shift = (uint32_t)k;
+  return f;
+}
+__device__ __forceinline__ int fd_div(int n, FastDiv f) {
+  return (int)(((unsigned long long)(uint32_t)n * f.mul) >> f.shift);
+}
+
+// Kernel parameters live in constant bank 0 and every launch gets a fresh copy, so an SM's first read of each 64-byte
+// line is a miss of ~0.4-0.5 us; the role loops read their fields one after another, which serialised three or four such
+// misses between griddepcontrol.wait and the first TMA issue (scripts/conv_chain_timeline.py: 1.1-1.9 us).  One warp
+// reads a word of every line up front -- independent loads with constant offsets (LDC), so the misses overlap and they
+// happen while the previous kernel is still draining.
+template <class T>
+__device__ __forceinline__ void warm_param_lines(const T& G) {
+  constexpr int kLines = (int)((sizeof(T) + 63) / 64);
+  const uint32_t* p = reinterpret_cast<const uint32_t*>(&G);
+  uint32_t acc = 0;
+#pragma unroll
+  for (int l = 0; l < kLines; ++l) acc ^= p[l * 16];
+  // a use ptxas cannot drop (an empty asm leaves the loads dead at the PTX level and they are removed)
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %0, 0xD1CEB00C;\n\t@p nanosleep.u32 1;\n\t}" ::"r"(acc));
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
 }
@@ -112,6 +148,8 @@ __device__ __forceinline__ float act_epi(float v, int act, float slope) {
   if (act == YB_ACT_LEAKY) return v > 0.f ? v : v * slope;
   return v;
 }
+// factor the kernels apply to the bias when they copy it into shared memory (see epi_bias_act)
+__device__ __forceinline__ float epi_bias_scale(int act) { return act == YB_ACT_SILU ? 0.5f : 1.0f; }
 // ---- epilogue: one 32-column TMEM chunk of one accumulator row -> bias + activation -> swizzled staging.
 // ACT is a template parameter so the 32 elements form one straight-line block (a per-element runtime
 // switch serialises the LDS -> FADD -> MUFU chains); the bias is read with 8 LDS.128.
@@ -123,8 +161,17 @@ __device__ __forceinline__ void epi_bias_act(const uint32_t (&v)[32], const floa
     const float bb[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
-      const float x = __uint_as_float(v[4 * j + e]) + bb[e];
-      f[4 * j + e] = ACT == YB_ACT_SILU ? silu_fast(x) : ACT == YB_ACT_LEAKY ? (x > 0.f ? x : x * slope) : x;
+      if (ACT == YB_ACT_SILU) {
+        // the kernels keep bias / 2 in shared memory for SiLU layers (epi_bias_scale): h = (acc + bias) / 2 is ONE FFMA,
+        // bit-identical to the add followed by the halving (a power-of-two scale commutes with the rounding)
+        const float h = fmaf(__uint_as_float(v[4 * j + e]), 0.5f, bb[e]);
+        float t;
+        asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+        f[4 * j + e] = fmaf(h, t, h);
+      } else {
+        const float x = __uint_as_float(v[4 * j + e]) + bb[e];
+        f[4 * j + e] = ACT == YB_ACT_LEAKY ? (x > 0.f ? x : x * slope) : x;
+      }
     }
   }
 }
