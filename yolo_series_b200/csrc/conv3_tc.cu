@@ -32,6 +32,7 @@ struct Conv3Args {
   int pair;                        // 1: CTA pairs (cta_group::2): M = 256 per MMA, each CTA holds half of every weight tile
   uint32_t a_bytes;                // slab bytes, rounded up to 1024
   uint32_t a_tx;                   // bytes the slab TMA actually delivers
+  unsigned long long* dbg;         // tuning aid: globaltimer stamps, 16 per CTA (tc_common.cuh YB_CTS)
   uint32_t idesc;
 };
 
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
   const bool leader = rank == 0u;
+  YB_CTS(0, threadIdx.x == 0);
   if (warp == 2) warm_param_lines(G);     // tc_common.cuh: parameter lines are cold per launch
   const uint32_t bn_cta = PAIR ? (uint32_t)G.BN / 2u : (uint32_t)G.BN;
   const uint32_t raw = smem_u32(smem_dyn);
@@ -136,6 +138,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
       if (first) {
         asm volatile("" ::"r"(n0), "r"(w0), "r"(h0), "r"(img));     // coordinates first, then the wait
         pdl_wait();                // activations written by the previous kernel are visible from here on
+        YB_CTS(2, lane == 0);
         first = false;
       }
       for (int kk = 0; kk < G.kchunks; ++kk) {
@@ -254,6 +257,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
     }
     if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem may go once it has been read; the writes complete with the grid
   }
+  YB_CTS(9, threadIdx.x == 64);     // an epilogue thread, after its last store has left shared memory
   if (PAIR) {
     // neither CTA may leave (or free TMEM) while the other can still signal its barriers or read its operands
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -403,6 +407,7 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
   const int walkers_max = A.pair ? num_sms() / 2 : num_sms();
   const int walkers = (int)(units < walkers_max ? units : walkers_max);
   P->grid = A.pair ? 2 * walkers : walkers;
+  A.dbg = conv_dbg_slot();
   *out = P;
   return YB_OK;
 }

@@ -33,12 +33,14 @@ struct ConvS2pArgs {
   int act; float slope;
   int bias_len, tmem_cols;
   uint32_t a_bytes, a_tx;          // stage bytes (1024-aligned, incl. the one-row overrun) / bytes TMA delivers
+  unsigned long long* dbg;         // tuning aid: globaltimer stamps, 16 per CTA (tc_common.cuh YB_CTS)
   uint32_t idesc;
 };
 
 __global__ void __launch_bounds__(kTcThreads, 1) k_conv3s2p_tc(const __grid_constant__ ConvS2pArgs G) {
   extern __shared__ unsigned char smem_dyn[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  YB_CTS(0, threadIdx.x == 0);
   if (warp == 2) warm_param_lines(G);     // tc_common.cuh: parameter lines are cold per launch
   const uint32_t raw = smem_u32(smem_dyn);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
@@ -90,6 +92,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3s2p_tc(const __grid_cons
   }
   pdl_launch_dependents();
   pdl_wait();
+  YB_CTS(2, threadIdx.x == 0);
   const int tiles_per_img = G.tiles_w * G.tiles_h;
   const int BW = G.BWS - 1;
   const uint32_t e_bytes = (uint32_t)(G.BH * G.BWS) * 128u;     // even-row part of the slab; odd rows follow
@@ -197,6 +200,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3s2p_tc(const __grid_cons
     else run(std::integral_constant<int, YB_ACT_NONE>{});
     if (store_thread) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem may go once it has been read; the writes complete with the grid
   }
+  YB_CTS(9, threadIdx.x == 64);
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -297,6 +301,7 @@ int conv3s2p_plan_create(const yb_conv_desc& d, ConvS2pPlan** out) {
   const long long total = (long long)A.tiles_w * A.tiles_h * x.N;
   A.total_tiles = (int)total;
   P->grid = (int)(total < num_sms() ? total : num_sms());
+  A.dbg = conv_dbg_slot();
   *out = P;
   return YB_OK;
 }

@@ -19,6 +19,16 @@
 
 namespace yb {
 
+unsigned long long* conv_dbg_slot() {
+  static long long next_slot = 0;
+  const char* ts = getenv("YB_CONV_TS");
+  if (!ts) return nullptr;
+  auto* base = reinterpret_cast<unsigned long long*>(strtoull(ts, nullptr, 0));
+  const char* st = getenv("YB_CONV_TS_STRIDE");
+  const long long stride = st ? strtoll(st, nullptr, 0) : 0;
+  return base + (stride > 0 ? stride * next_slot++ : 0);
+}
+
 struct ConvTcArgs {
   CUtensorMap tm_a;
   CUtensorMap tm_b;
@@ -51,16 +61,6 @@ struct ConvTcArgs {
   unsigned long long* dbg;         // tuning aid (env YB_CONV_TS = device address): globaltimer stamps, 16 per CTA
 };
 
-// stamp `slot` of this CTA's 16-entry row from one thread when the debug buffer is set (scripts/conv_timeline.py,
-// scripts/conv_chain_timeline.py; the buffer holds 16 x grid entries)
-#define YB_CTS(slot, cond)                                                                                  \
-  do {                                                                                                      \
-    if (G.dbg && (cond)) {                                                                                  \
-      unsigned long long t_;                                                                                \
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                \
-      G.dbg[blockIdx.x * 16 + slot] = t_;                                                                   \
-    }                                                                                                       \
-  } while (0)
 
 // Persistent kernel: one CTA per SM walks tiles t = blockIdx.x, +gridDim.x, ...  The TMA producer runs
 // ahead across tile boundaries (smem ring of `stages` K-chunks), accumulators are double-buffered in
@@ -402,6 +402,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     else run(std::integral_constant<int, YB_ACT_NONE>{});
     if ((ew & 3) == 0 && lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // smem may go once it has been read; the writes complete with the grid
     YB_CTS(8, warp == 2 && lane == 0);
+    YB_CTS(9, warp == 2 && lane == 0);     // (pair mode returns before the stamp at the end)
   }
   if (PAIR) {
     // neither CTA may leave (or free TMEM) while the other can still signal its barriers or read its operands
@@ -420,7 +421,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)G.tmem_cols)
                  : "memory");
   }
-  YB_CTS(9, threadIdx.x == 32);
 }
 
 struct ConvTcPlan {
@@ -463,7 +463,9 @@ static void pick_tile(int cout, long long m_tiles, int chunks, int bk, int y_es,
     // layers, where the extra cluster handshakes are not amortised; with fewer tiles than SMs they only pay off for
     // very long K.
     const long long k_total = (long long)chunks * bk;
-    pair_mode = (k_total >= 1024 && (k_total >= 4096 || m_tiles >= num_sms())) ? 1 : -1;
+    // (profiles/round2_tile_sweep.txt: with fewer M tiles than SMs pairs still win 3-7 % once K >= 2048 or Cout spans
+    // two or more 256-wide tiles; a single N tile at 20 x 20 loses)
+    pair_mode = (k_total >= 1024 && (k_total >= 2048 || m_tiles >= num_sms() || cout > 256)) ? 1 : -1;
   }
   int best = 64, best_res = 0, best_pair = 0;
   double best_cost = 1e30;
@@ -533,7 +535,6 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   ConvTcArgs& A = P->args;
   memset(&A, 0, sizeof(A));
   A.bias = d.bias; A.bias_len = d.cout_pad;
-  if (const char* ts = getenv("YB_CONV_TS")) A.dbg = reinterpret_cast<unsigned long long*>(strtoull(ts, nullptr, 0));
   // pair view (see k_repack_pair): needs pixel pairs to be contiguous in memory
   const bool pair_view = k == 3 && s == 2 && x.C == 32 && x.c_stride == 32 && x.W % 2 == 0 && ups == 1 && d.tile_n >= 0;
   int Cin = x.C, cin_pad = d.cin_pad, xW = x.W, x_cs = x.c_stride;
@@ -718,6 +719,7 @@ int conv_tc_plan_create(const yb_conv_desc& d, ConvTcPlan** out) {
   if (A.resident) walkers = walkers / A.tiles_n * A.tiles_n;
   YB_CHECK_ARG(walkers >= 1, "conv(tc): no walker fits the resident layout");
   P->grid = A.pair ? 2 * walkers : walkers;
+  A.dbg = conv_dbg_slot();
   *out = P;
   return YB_OK;
 }

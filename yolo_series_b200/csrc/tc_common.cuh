@@ -40,6 +40,21 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t src
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
                ::"l"(tm), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
+// stamp `slot` of this CTA's 16-entry row from one thread when the debug buffer is set (scripts/conv_timeline.py,
+// scripts/conv_chain_timeline.py; the buffer holds 16 x grid entries)
+#define YB_CTS(slot, cond)                                                                                  \
+  do {                                                                                                      \
+    if (G.dbg && (cond)) {                                                                                  \
+      unsigned long long t_;                                                                                \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                \
+      G.dbg[blockIdx.x * 16 + slot] = t_;                                                                   \
+    }                                                                                                       \
+  } while (0)
+// Debug buffer of a newly created plan (host side; NULL without the env).  YB_CONV_TS = device address; with
+// YB_CONV_TS_STRIDE = entries per plan every successfully created plan takes the next slot (creation order = the
+// engine's op order), which gives a timeline of a whole graph replay (scripts/step_timeline.py).
+unsigned long long* conv_dbg_slot();
+
 // Division of a tile index by a launch constant: n / d = (n * mul) >> shift for 0 <= n <= 2^30 with mul = ceil(2^k / d),
 // k = 31 + floor(log2 d) (the error term n * (mul * d - 2^k) stays below 2^k).  A runtime 32-bit division is ~30
 // dependent instructions; the role warps decompose a tile index with three or four of them per tile, which a lone warp
