@@ -316,6 +316,8 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--batch', type=int, default=BATCH, help='images per GPU per step')
     ap.add_argument('--no-extras', action='store_true', help='skip cpu_baseline / NMS stress / per-op profile')
+    ap.add_argument('--streams', type=int, default=2, choices=[1, 2],
+                    help='batches in flight on one GPU: 2 = consecutive steps alternate between two streams / engines')
     # secondary BASELINE.json configs (configs[2], configs[3]); the defaults are the headline workload
     ap.add_argument('--model', default=MODEL, help='cfg name (yolov7 | yolov7-tiny | yolov7-w6-custom | yolov7-e6e)')
     ap.add_argument('--img', type=int, default=IMG)
@@ -356,20 +358,35 @@ def main():
     # N > 1: the one exchange of the path (every rank's detections to every rank) happens inside the NMS kernel through
     # peer-to-peer stores over NVLink (dist.PeerGather); YB_GATHER=nccl selects the plain NCCL all-gather instead.
     use_peer = world > 1 and os.environ.get('YB_GATHER', 'peer') != 'nccl'
-    pg = None
+    pg = pg2 = None
     if use_peer:
         try:
             pg = ydist.PeerGather(B, MAX_DET, device=dev)
+            pg2 = ydist.PeerGather(B, MAX_DET, device=dev)     # one per compute stream (its slot protocol is per stream)
         except RuntimeError as ex:          # raised on every rank together: CUDA IPC unavailable -> NCCL all-gather
-            use_peer = False
+            use_peer, pg, pg2 = False, None, None
             if rank == 0:
                 print(f'[bench] {ex}', file=sys.stderr)
+    # Two batches in flight (args.streams = 2): consecutive steps are independent, so step k+1 runs on a second stream
+    # with its own engine and its CTAs take the SMs that step k's persistent kernels leave idle (last rounds, dependent
+    # launches, the 32-CTA NMS).  Every step is still one full pass over one batch; --streams 1 = strictly serial.
+    n_streams = args.streams if (world == 1 or use_peer) else 1
+    side = model.compute_streams(n_streams, dev) if n_streams > 1 else None
+    pgs = [pg, pg2]
 
-    def step_device():
-        out, meta = model.detect(x_dev, CONF, IOU, max_det=MAX_DET, packed=True, gather=pg)
-        if world > 1 and pg is None:
-            out, cnt = ydist.gather_detections(out, meta[:B])
-        return out, meta
+    def step_device(k=0, serial=False):
+        if side is None or serial:
+            out, meta = model.detect(x_dev, CONF, IOU, max_det=MAX_DET, packed=True, gather=pg)
+            if world > 1 and pg is None:
+                out, cnt = ydist.gather_detections(out, meta[:B])
+            return out, meta
+        with torch.cuda.stream(side[k % n_streams]):
+            return model.detect(x_dev, CONF, IOU, max_det=MAX_DET, packed=True, gather=pgs[k % n_streams])
+
+    def join_streams():
+        if side is not None:
+            for st in side:
+                torch.cuda.current_stream().wait_stream(st)
 
     def step_e2e():
         # the pinned host batch is copied H2D straight into the engine's input buffer, every step
@@ -387,15 +404,25 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    for _ in range(max(args.warmup, 3)):
-        step_device()
+    for k in range(max(args.warmup, 3) * n_streams):
+        step_device(k)
+    for _ in range(3):
+        step_device(serial=True)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # strictly serial steps on one stream first (reported as value_one_stream; the per-kernel rooflines refer to it)
+    e0.record()
+    for _ in range(args.steps):
+        step_device(serial=True)
+    e1.record()
+    barrier()
+    ms_serial = e0.elapsed_time(e1)
     barrier()
     t_wall0 = time.time()
     e0.record()
-    for _ in range(args.steps):
-        out, meta = step_device()
+    for k in range(args.steps):
+        out, meta = step_device(k)
+    join_streams()
     e1.record()
     barrier()
     sampler.window(t_wall0, time.time())
@@ -417,7 +444,8 @@ def main():
 
     def run_stream(n):
         last = None
-        for last in model.detect_batches((x_host for _ in range(n)), CONF, IOU, max_det=MAX_DET, post=post, gather=pg):
+        for last in model.detect_batches((x_host for _ in range(n)), CONF, IOU, max_det=MAX_DET, post=post,
+                                         gather=pg, compute_streams=1):
             pass
         return last
     run_stream(3)
@@ -428,9 +456,9 @@ def main():
     barrier()
     ms_e2e = e0.elapsed_time(e1)
     if world > 1:
-        t = torch.tensor([ms_dev, ms_e2e, ms_e2e_serial], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms_dev, ms_e2e, ms_e2e_serial, ms_serial], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_dev, ms_e2e, ms_e2e_serial = float(t[0]), float(t[1]), float(t[2])
+        ms_dev, ms_e2e, ms_e2e_serial, ms_serial = float(t[0]), float(t[1]), float(t[2]), float(t[3])
     # ---- N > 1: correctness of the exchange, outside the timed region.  Rank 0 regenerates every rank's seeded shard,
     # runs it through its own replica (no gather) and compares with the block that arrived for that rank.
     gather_check = None
@@ -456,13 +484,15 @@ def main():
             gather_check = 'bit-identical' if ok else 'MISMATCH'
         barrier()
     if pg is not None:
-        pg.check()
-        pg.close()
+        for g in (pg, pg2):
+            g.check()
+            g.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    eng = next(iter(model._engines.values()))
+    eng = model.run_trunk(x_dev)         # the engine of the main stream (per-op profile, serial trunk / NMS times)
+    torch.cuda.synchronize()
     n_imgs = B * world * args.steps
     launches_per_step = 1 + eng.num_launches() + 2     # stage + trunk ops + k_filter + k_sort_nms
     line = {
@@ -471,10 +501,15 @@ def main():
         'ms_per_step': ms_dev / args.steps, 'higher_is_better': True, 'scaling': scaling, 'vs_baseline': None,
         'dtype': 'bf16', 'data': 'synthetic',
         'value_note': 'inputs resident in HBM (uint8 batch on the device); the host-to-host figure is e2e.value',
+        'value_one_stream': n_imgs / (ms_serial / 1e3), 'ms_per_step_one_stream': ms_serial / args.steps,
         'config': {'workload': workload_name(model_name, img, B),
                    'batch_per_gpu': B, 'global_batch': B * world, 'parallelism': f'image-sharded replicas x{world}',
                    'gather': ('none' if world == 1 else 'in-kernel P2P stores over NVLink (yb_decode_nms_gather)' if use_peer
                               else 'NCCL all_gather'),
+                   'streams': n_streams,
+                   'in_flight': (f'{n_streams} batches in flight: steps alternate between {n_streams} streams, one engine '
+                                 'each; every step is one full pass over one batch (value_one_stream = strictly serial)'
+                                 if n_streams > 1 else 'strictly serial steps on one stream'),
                    'l2': 'no flush: per-step working set (activations, GBs) >> 126 MB L2',
                    'input': 'one seeded pinned uint8 batch per rank, re-sent H2D every e2e step'},
         'e2e': {'value': n_imgs / (ms_e2e / 1e3), 'unit': 'images/s', 'h2d_bytes_per_step': x_host.numel(),

@@ -136,6 +136,43 @@ def test_detect_batches_stream_equals_detect():
     assert list(m.detect_batches(iter([]), 0.05, 0.5)) == []
 
 
+def test_two_batches_in_flight_equal_serial_results():
+    """Engines and NMS scratch are per stream: two streams running Model.detect at the same time (what
+    detect_batches(compute_streams=2) and bench.py --streams 2 do) give, batch by batch, exactly the serial results --
+    a shared activation arena or workspace would corrupt them."""
+    m = _build('yolov7-tiny', 'bf16')
+    xs = [synth_image(8, 256, 320, seed=40 + i, dtype=torch.uint8).cuda() for i in range(10)]
+    want = []
+    for x in xs:
+        out, meta = m.detect(x, 0.05, 0.5, max_det=100, packed=True)
+        want.append((out.clone(), meta.clone()))
+    torch.cuda.synchronize()
+    side = m.compute_streams(2)
+    assert side[0] is m.compute_streams(2)[0] and side[0].cuda_stream != side[1].cuda_stream
+    got = []
+    for rep in range(3):                     # back to back, no host synchronisation between the calls
+        got = []
+        for i, x in enumerate(xs):
+            with torch.cuda.stream(side[i & 1]):
+                got.append(m.detect(x, 0.05, 0.5, max_det=100, packed=True))
+    torch.cuda.synchronize()
+    keys = {k[-1] for k in m._engines}
+    assert {side[0].cuda_stream, side[1].cuda_stream} <= keys          # one engine per stream
+    for (o, me), (wo, wm) in zip(got, want):
+        assert torch.equal(me, wm) and int(me[-1]) == 0
+        for i in range(o.shape[0]):
+            assert torch.equal(o[i, :int(me[i])], wo[i, :int(me[i])])
+    # the streaming API on one and on two compute streams
+    host = [x.cpu().pin_memory() for x in xs]
+    one = [(o.clone(), c.clone()) for o, c in m.detect_batches(iter(host), 0.05, 0.5, max_det=100, compute_streams=1)]
+    two = [(o.clone(), c.clone()) for o, c in m.detect_batches(iter(host), 0.05, 0.5, max_det=100, compute_streams=2)]
+    assert len(one) == len(two) == len(xs)
+    for (o1, c1), (o2, c2), (wo, wm) in zip(one, two, want):
+        assert torch.equal(c1, c2) and torch.equal(c1, wm[:-1].cpu())
+        for i in range(o1.shape[0]):
+            assert torch.equal(o1[i, :c1[i]], o2[i, :c1[i]]) and torch.equal(o1[i, :c1[i]], wo[i, :c1[i]].cpu())
+
+
 def test_peer_gather_single_rank_equals_detect():
     """The gather fused into the NMS kernel (yb_decode_nms_gather + yb_peer_wait, dist.PeerGather) on a one-rank group:
     rows go through the peer-store path into the (self-mapped) receive buffer, both buffer sets are exercised and the

@@ -243,7 +243,9 @@ class Model(nn.Module):
     def _get_engine(self, B, H, W, device, img_dtype=torch.uint8):
         if device.index is None:
             device = torch.device('cuda', torch.cuda.current_device())
-        key = (B, H, W, str(device), self._compute_dtype, img_dtype)
+        # an engine owns its activation buffers, so calls issued on different streams must not share one: the key
+        # carries the current stream (two batches in flight = two engines; the packed weights are shared)
+        key = (B, H, W, str(device), self._compute_dtype, img_dtype, torch.cuda.current_stream(device).cuda_stream)
         eng = self._engines.get(key)
         if eng is None:
             if getattr(self, '_lowered', None) is None:
@@ -252,6 +254,7 @@ class Model(nn.Module):
                                                fused=self._is_ref_fused())
             while len(self._engines) >= max(1, int(self.engine_cache_size)):
                 _, old = self._engines.popitem(last=False)       # least recently used
+                torch.cuda.synchronize(device)                   # it may still be running on another stream
                 old.destroy()
             if not hasattr(self, '_packed'):
                 self._packed = {}
@@ -266,6 +269,17 @@ class Model(nn.Module):
     def _device(self):
         p = next(self.parameters())
         return p.device
+
+    def compute_streams(self, n, device=None):
+        """``n`` side streams of ``device``, created once per model (engines are cached per stream, so the streams have
+        to be the same objects from call to call)."""
+        dev = device if device is not None else self._device()
+        if dev.index is None:
+            dev = torch.device('cuda', torch.cuda.current_device())
+        pool = self.__dict__.setdefault('_side_streams', {}).setdefault(str(dev), [])
+        while len(pool) < n:
+            pool.append(torch.cuda.Stream(dev))
+        return pool[:n]
 
     def head_levels(self, eng):
         head = self._layers()[-1]
@@ -443,25 +457,38 @@ class Model(nn.Module):
 
     @torch.no_grad()
     def detect_batches(self, batches, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False,
-                       multi_label=False, max_det=300, max_nms=30000, post=None, gather=None):
+                       multi_label=False, max_det=300, max_nms=30000, post=None, gather=None, compute_streams=None):
         """Streaming form of ``detect`` for host batches (the detect.py:87-152 loop over a dataset): a generator that
         takes (B, 3, H, W) uint8/float32 HOST tensors (pinned for real overlap) and yields, in order, one
         ``(out (B', max_det, 6) fp32, counts (B',) int32)`` pair of pinned HOST tensors per batch.
 
-        Three streams, two slots: batch i+1's H2D copy and batch i-1's D2H read run on their own copy streams
-        while batch i computes on the caller's stream, so PCIe time leaves the critical path; each step still
-        moves its own input H2D and its own result D2H.  ``post(out, counts) -> (out, counts)`` runs on the compute
-        stream before the read-back (e.g. ``dist.gather_detections``); ``gather`` (a ``dist.PeerGather``) does the multi-GPU
-        exchange inside the NMS kernel instead and every yielded pair then covers the global batch.  A yielded pair stays valid until the next
-        batch is drawn (its pinned buffers are reused two batches later)."""
+        Copy streams, two (three) slots: batch i+1's H2D copy and batch i-1's D2H read run on their own copy streams
+        while batch i computes, so PCIe time leaves the critical path; each step still moves its own input H2D and its
+        own result D2H.  ``compute_streams`` = 1 (default) computes on the caller's stream; 2 alternates the batches
+        between two side streams with one engine each (three slots): consecutive batches are independent, so the CTAs
+        of batch i+1 fill the SMs that batch i's persistent kernels leave idle in their last round and between
+        dependent launches.  Measured with device-resident inputs: +2.5-3 % images/s at batch 32, +57 % at batch 1
+        (`scripts/two_stream_probe.py`); through this host pipeline at batch 32 the two settings are equal, hence the
+        default.  A ``dist.PeerGather``'s slot protocol is ordered by ONE stream: pass one gather per compute stream.
+        ``post(out, counts) -> (out, counts)`` runs on the compute stream before the read-back (e.g.
+        ``dist.gather_detections``); ``gather`` (a ``dist.PeerGather``, or one per compute stream) does the multi-GPU
+        exchange inside the NMS kernel instead and every yielded pair then covers the global batch.  A yielded pair
+        stays valid until the next batch is drawn (its pinned buffers are reused two or three batches later)."""
         from collections import deque
         dev = self._device()
         if dev.type != 'cuda':
             raise RuntimeError('yolo_series_b200.Model needs a CUDA device (no CPU fallback)')
         main = torch.cuda.current_stream(dev)
+        gathers = list(gather) if isinstance(gather, (list, tuple)) else [gather]
+        if compute_streams is None:
+            compute_streams = 1
+        if compute_streams not in (1, 2) or (gathers[0] is not None and len(gathers) < compute_streams):
+            raise ValueError('compute_streams must be 1 or 2, with one PeerGather per compute stream')
+        cstreams = [main] if compute_streams == 1 else self.compute_streams(2, dev)
         h2d, d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
         slots = [dict(stage=None, host=None, consumed=torch.cuda.Event(), loaded=torch.cuda.Event(),
-                      done=torch.cuda.Event(), read=torch.cuda.Event(), used=False) for _ in range(2)]
+                      done=torch.cuda.Event(), read=torch.cuda.Event(), used=False, gather=None)
+                 for _ in range(compute_streams + 1)]      # one more slot than batches computing: the next H2D runs ahead
         pending = deque()
 
         def finish(s):
@@ -470,14 +497,14 @@ class Model(nn.Module):
             B = meta.numel() - 1
             if int(meta[B]) != 0:
                 raise RuntimeError('yb_nms: candidate capacity exceeded (YB_ERR_OVERFLOW)')
-            if gather is not None:
-                gather.raise_if_poisoned(meta[:B])
+            if s['gather'] is not None:
+                s['gather'].raise_if_poisoned(meta[:B])
             s['keep'] = None
             return s['host'][0], meta[:B]
 
         for i, xb in enumerate(batches):
-            s = slots[i & 1]
-            if len(pending) == 2:
+            s = slots[i % len(slots)]
+            if len(pending) == len(slots):
                 yield finish(pending.popleft())
             if s['stage'] is None or s['stage'].shape != xb.shape or s['stage'].dtype != xb.dtype:
                 s['stage'] = torch.empty(xb.shape, dtype=xb.dtype, device=dev)
@@ -486,15 +513,20 @@ class Model(nn.Module):
             with torch.cuda.stream(h2d):
                 s['stage'].copy_(xb, non_blocking=True)
                 s['loaded'].record(h2d)
-            main.wait_event(s['loaded'])
-            out, meta = self.detect(s['stage'], conf_thres, iou_thres, classes, agnostic, multi_label, max_det,
-                                    max_nms, packed=True, gather=gather)
-            s['consumed'].record(main)
-            ovf = meta[-1:]
-            if post is not None:
-                out, cnt = post(out, meta[:-1])
-                meta = torch.cat((cnt.to(torch.int32), ovf))
-            s['done'].record(main)
+            cs = cstreams[(i & 1) % len(cstreams)]
+            g = gathers[(i & 1) % len(gathers)]
+            cs.wait_event(s['loaded'])
+            if s['used']:
+                cs.wait_event(s['read'])         # the slot's previous result has left the device
+            with torch.cuda.stream(cs):
+                out, meta = self.detect(s['stage'], conf_thres, iou_thres, classes, agnostic, multi_label, max_det,
+                                        max_nms, packed=True, gather=g)
+                s['consumed'].record(cs)
+                ovf = meta[-1:]
+                if post is not None:
+                    out, cnt = post(out, meta[:-1])
+                    meta = torch.cat((cnt.to(torch.int32), ovf))
+                s['done'].record(cs)
             if s['host'] is None or s['host'][0].shape != out.shape:
                 s['host'] = (torch.empty(out.shape, dtype=out.dtype).pin_memory(),
                              torch.empty(meta.shape, dtype=meta.dtype).pin_memory())
@@ -504,7 +536,7 @@ class Model(nn.Module):
                 s['host'][1].copy_(meta, non_blocking=True)
                 s['read'].record(d2h)
             s['keep'] = (out, meta)          # device results stay referenced until the read-back has completed
-            s['used'] = True
+            s['used'], s['gather'] = True, g
             pending.append(s)
         while pending:
             yield finish(pending.popleft())

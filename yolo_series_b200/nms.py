@@ -14,7 +14,11 @@ from . import _lib
 _ws_cache = {}
 
 
-def _workspace(nbytes, device, slot=0):
+def _workspace(nbytes, device, slot=None):
+    """Scratch buffer of the calling stream: two streams may run the NMS kernels at the same time (Model.detect_batches
+    keeps two batches in flight), so the cache is keyed by (device, current stream)."""
+    if slot is None:
+        slot = torch.cuda.current_stream(device).cuda_stream
     key = (str(device), slot)
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:
