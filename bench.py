@@ -445,7 +445,8 @@ def main():
     def run_stream(n):
         last = None
         for last in model.detect_batches((x_host for _ in range(n)), CONF, IOU, max_det=MAX_DET, post=post,
-                                         gather=pg, compute_streams=1):
+                                         gather=(pgs if (pg is not None and n_streams == 2) else pg),
+                                         compute_streams=n_streams):
             pass
         return last
     run_stream(3)
@@ -514,7 +515,7 @@ def main():
                    'input': 'one seeded pinned uint8 batch per rank, re-sent H2D every e2e step'},
         'e2e': {'value': n_imgs / (ms_e2e / 1e3), 'unit': 'images/s', 'h2d_bytes_per_step': x_host.numel(),
                 'd2h_bytes_per_step': int(res.numel() * 4 + cnt.numel() * 4 + 4), 'ms_per_step': ms_e2e / args.steps,
-                'api': 'Model.detect_batches (H2D / compute / D2H on three streams, two slots)',
+                'api': f'Model.detect_batches (H2D / D2H copy streams + {n_streams} compute stream(s), {2 if n_streams == 1 else 6} slots)',
                 'serial_value': n_imgs / (ms_e2e_serial / 1e3),
                 'serial_api': 'Model.detect(x_host) + .cpu() per step, one stream'},
         'gpu_launches': launches_per_step * args.steps,

@@ -462,33 +462,34 @@ class Model(nn.Module):
         takes (B, 3, H, W) uint8/float32 HOST tensors (pinned for real overlap) and yields, in order, one
         ``(out (B', max_det, 6) fp32, counts (B',) int32)`` pair of pinned HOST tensors per batch.
 
-        Copy streams, two (three) slots: batch i+1's H2D copy and batch i-1's D2H read run on their own copy streams
+        Copy streams and slots: batch i+1's H2D copy and batch i-1's D2H read run on their own copy streams
         while batch i computes, so PCIe time leaves the critical path; each step still moves its own input H2D and its
-        own result D2H.  ``compute_streams`` = 1 (default) computes on the caller's stream; 2 alternates the batches
-        between two side streams with one engine each (three slots): consecutive batches are independent, so the CTAs
-        of batch i+1 fill the SMs that batch i's persistent kernels leave idle in their last round and between
-        dependent launches.  Measured with device-resident inputs: +2.5-3 % images/s at batch 32, +57 % at batch 1
-        (`scripts/two_stream_probe.py`); through this host pipeline at batch 32 the two settings are equal, hence the
-        default.  A ``dist.PeerGather``'s slot protocol is ordered by ONE stream: pass one gather per compute stream.
+        own result D2H.  ``compute_streams`` = 2 (the default without ``post`` / with no or two ``gather`` objects)
+        alternates the batches between two side streams with one engine each and six slots: consecutive batches are
+        independent, so the CTAs of batch i+1 fill the SMs that batch i's persistent kernels leave idle in their last
+        round and between dependent launches -- +2.4 % images/s at batch 32 (`scripts/e2e_streams_probe.py`; two or
+        three slots are too shallow: the host then enqueues a batch only when both streams are about to drain), ~+60 %
+        at batch 1 (`scripts/two_stream_probe.py`).  1 computes on the caller's stream with two slots.  A
+        ``dist.PeerGather``'s slot protocol is ordered by ONE stream: pass one gather per compute stream.
         ``post(out, counts) -> (out, counts)`` runs on the compute stream before the read-back (e.g.
         ``dist.gather_detections``); ``gather`` (a ``dist.PeerGather``, or one per compute stream) does the multi-GPU
         exchange inside the NMS kernel instead and every yielded pair then covers the global batch.  A yielded pair
-        stays valid until the next batch is drawn (its pinned buffers are reused two or three batches later)."""
+        stays valid until the next batch is drawn (its pinned buffers are reused two -- or six -- batches later)."""
         from collections import deque
         dev = self._device()
         if dev.type != 'cuda':
             raise RuntimeError('yolo_series_b200.Model needs a CUDA device (no CPU fallback)')
         main = torch.cuda.current_stream(dev)
         gathers = list(gather) if isinstance(gather, (list, tuple)) else [gather]
-        if compute_streams is None:
-            compute_streams = 1
+        if compute_streams is None:      # a PeerGather's slot protocol is ordered by ONE stream: one gather per stream
+            compute_streams = 2 if (post is None and (gather is None or len(gathers) == 2)) else 1
         if compute_streams not in (1, 2) or (gathers[0] is not None and len(gathers) < compute_streams):
             raise ValueError('compute_streams must be 1 or 2, with one PeerGather per compute stream')
         cstreams = [main] if compute_streams == 1 else self.compute_streams(2, dev)
         h2d, d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
         slots = [dict(stage=None, host=None, consumed=torch.cuda.Event(), loaded=torch.cuda.Event(),
                       done=torch.cuda.Event(), read=torch.cuda.Event(), used=False, gather=None)
-                 for _ in range(compute_streams + 1)]      # one more slot than batches computing: the next H2D runs ahead
+                 for _ in range(2 if compute_streams == 1 else 6)]
         pending = deque()
 
         def finish(s):
