@@ -243,6 +243,42 @@ def test_conv3_slab_cta_pairs(case):
     assert torch.equal(y1, y2)
 
 
+WIDE_CASES = [
+    # (N, H, W, Cin, Cout, act, tile_n): 3x3 stride-1 layers through the wide-slab kernel (YB_C3_WIDE=1 takes every shape)
+    (1, 160, 160, 64, 64, 1, 0),          # N = 64, two stacked sub-tiles, many rounds
+    (2, 40, 40, 128, 128, 1, 0),          # N = 128, two K chunks
+    (1, 80, 80, 64, 192, 1, 64),          # three N tiles of 64
+    (3, 12, 20, 96, 96, 1, 0),            # ragged tiles in both directions, Cin 96: the second K chunk is half out of bounds
+    (2, 24, 24, 512, 64, 1, 0),           # 8 K chunks: slab and weight rings wrap several times per tile
+    (1, 8, 8, 64, 64, 1, 0),              # a single tile, mostly halo
+    (2, 33, 17, 128, 255, 2, 0),          # odd sizes, Cout 255 (head-like), LeakyReLU
+    (1, 20, 20, 256, 256, 0, 0),          # the small map the rule declines, no activation
+]
+
+
+@pytest.mark.parametrize('case', WIDE_CASES, ids=[str(c) for c in WIDE_CASES])
+def test_conv3_wide_slab_equals_slab_kernel(case, monkeypatch):
+    """k_conv3w_tc (one activation slab per K chunk, filter taps as descriptor offsets into rows of 10 pixels, group stride
+    1280 B) against k_conv3_tc (one slab per filter column): the MMAs accumulate in the same order, so the outputs must
+    be bit-identical; both within bf16 tolerance of the fp32 PyTorch reference."""
+    from yolo_series_b200 import ops
+    N, H, W, Ci, Co, act, tn = case
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn((N, Ci, H, W), generator=g).bfloat16().float()
+    w = (torch.randn((Co, Ci, 3, 3), generator=g) / (Ci * 9) ** 0.5).bfloat16().float()
+    b = torch.randn((Co,), generator=g)
+    ref = _ref_conv(x, w, b, 1, act, 0.1, 1)
+    xd = _nhwc(x).cuda().bfloat16()
+    monkeypatch.setenv('YB_C3_WIDE', '0')
+    y_old = ops.conv2d(xd, w, b, 1, act, 0.1, 1, tile_n=tn, pair=-1)
+    monkeypatch.setenv('YB_C3_WIDE', '1')
+    y_new = ops.conv2d(xd, w, b, 1, act, 0.1, 1, tile_n=tn, pair=-1)
+    torch.cuda.synchronize()
+    got = _nchw(y_new[..., :Co].float().cpu())
+    assert torch.allclose(got, ref, rtol=1.2e-2, atol=1.2e-2), float((got - ref).abs().max())
+    assert torch.equal(y_old[..., :Co], y_new[..., :Co])
+
+
 POOL_CASES = [
     # (N, H, W, Cin, Cout, k, s, act, tile_n, pair)
     (2, 40, 40, 64, 64, 1, 1, 1, 0, 0),         # 1x1, one 64-channel group, several tiles per image

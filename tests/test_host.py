@@ -58,6 +58,52 @@ def test_lowering_statistics():
         assert c[_lib.OP_COPY] == 0 and c[_lib.OP_UPSAMPLE2] == 0     # concat + upsample fully planned away
 
 
+def test_epilogue_fusion_pass_folds_pools_and_shortcuts(monkeypatch):
+    """Engine._fuse_elementwise (host logic, no GPU): in the bf16 path every Shortcut add moves into the conv that is
+    computed later (models/common.py:80-86) and every 2x2 max-pool behind a 1x1 conv into that conv (common.py:30-36);
+    the fp32 parity mode and YB_NO_EPILOGUE_FUSION keep the lowered list; the shared lowered graph is not modified."""
+    from collections import Counter
+
+    import torch
+
+    from yolo_series_b200.engine import Engine
+    # (ops after fusion, pools fused, adds fused, pools left)
+    want = {'yolov7': (85, 5, 0, 0), 'yolov7-tiny': (51, 3, 0, 0), 'yolov7-w6-custom': (97, 0, 0, 0),
+            'yolov7-e6e': (224, 7, 11, 1)}
+    for name, (nops, npool, nadd, pools_left) in want.items():
+        L = plan.lower(Model(name).model, 3)
+        before = list(L.ops)
+        ops, pool_of = Engine._fuse_elementwise(L, torch.bfloat16)
+        assert L.ops == before                                       # engines of one model share the lowered graph
+        c = Counter(o.kind for o in ops)
+        assert (len(ops), len(pool_of), c[_lib.OP_ADD], c[_lib.OP_MAXPOOL2]) == (nops, npool, 0, pools_left), name
+        res = [o for o in ops if o.kind == _lib.OP_CONV and len(o.ins) == 2]
+        assert len(res) == nadd
+        for o in res:                                                # a residual conv is 1x1, bf16 out, no upsample
+            assert o.conv.k == 1 and o.upsample == 1 and not L.vals[o.outs[0]].f32 and o.name.endswith('+add')
+            assert L.vals[o.ins[1]].C == o.conv.c_out                # the other term has the conv's width
+        made_at = {}                                                 # value id -> index of the op that writes it
+        for i, o in enumerate(ops):
+            for v in list(o.outs) + ([pool_of[id(o)]] if id(o) in pool_of else []):
+                made_at[v] = i
+        for i, o in enumerate(ops):                                  # the residual term is ready when its conv runs
+            if o in res:
+                assert made_at[o.ins[1]] < i, (name, o.name)
+        for o in before:                                             # what a removed pool produced is still produced
+            if o.kind == _lib.OP_MAXPOOL2 and o not in ops:
+                assert o.outs[0] in pool_of.values()
+        for cid, pv in pool_of.items():
+            conv = next(o for o in ops if id(o) == cid)
+            full = L.vals[conv.outs[0]]
+            assert conv.conv.k == 1 and L.vals[pv].den == 2 * full.den and L.vals[pv].C == full.C
+        ops32, pool32 = Engine._fuse_elementwise(L, torch.float32)
+        assert ops32 == before and pool32 == {}
+    L = plan.lower(Model('yolov7-e6e').model, 3)
+    monkeypatch.setenv('YB_NO_EPILOGUE_FUSION', '1')
+    ops, pool_of = Engine._fuse_elementwise(L, torch.bfloat16)
+    assert len(ops) == len(L.ops) == 242 and pool_of == {}
+
+
 def _run_lowered_cpu(L, x):
     """Interpret the lowered op list with torch CPU ops (test-only) to validate fold + placement logic."""
     vals = {}

@@ -120,6 +120,11 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out);
 int conv3_tc_launch(const Conv3Plan* p, cudaStream_t s);
 void conv3_tc_plan_destroy(Conv3Plan* p);
 
+const char* conv3_tc_kernel_name(const Conv3Plan* p);   // "k_conv3_tc" or "k_conv3w_tc" (the wide-slab variant it may hold)
+struct Conv3wPlan;   // 3x3 stride-1 wide-slab kernel (conv3w_tc.cu): one activation slab per K chunk; held by Conv3Plan
+int conv3w_plan_create(const yb_conv_desc& d, int force, Conv3wPlan** out);
+int conv3w_launch(const Conv3wPlan* p, cudaStream_t s);
+void conv3w_plan_destroy(Conv3wPlan* p);
 struct ConvS2pPlan;  // 3x3 stride-2 pair-slab kernel for 32-channel inputs (conv3s2p_tc.cu)
 int conv3s2p_plan_create(const yb_conv_desc& d, ConvS2pPlan** out);
 int conv3s2p_launch(const ConvS2pPlan* p, cudaStream_t s);

@@ -281,7 +281,11 @@ struct Conv3Plan {
   Conv3Args args;
   int grid;
   size_t smem;
+  Conv3wPlan* wide = nullptr;      // set: the layer runs on the wide-slab kernel (conv3w_tc.cu) instead
+  ~Conv3Plan() { if (wide) conv3w_plan_destroy(wide); }
 };
+
+const char* conv3_tc_kernel_name(const Conv3Plan* p) { return p->wide ? "k_conv3w_tc" : "k_conv3_tc"; }
 
 // Returns YB_ERR_UNSUPPORTED (without touching the error string semantics of real failures) when the shape
 // is better served by the generic kernel; the caller then falls back to conv_tc.
@@ -298,6 +302,18 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
   Conv3Plan* P = new Conv3Plan();
   Conv3Args& A = P->args;
   memset(&A, 0, sizeof(A));
+  {   // The wide-slab kernel (conv3w_tc.cu: one activation slab per K chunk instead of three) is OPT-IN: YB_C3_WIDE = 1
+      // takes every shape it can run, 2 only maps it tiles without waste.  Measured (profiles/README.md, round 2): 4 %
+      // faster on the isolated 64 -> 64 layers, 7-9 % slower where this kernel runs as CTA pairs (Cin >= 128), and in
+      // the network 0.7 % (rule 2) to 2.6 % SLOWER at batch 32 -- so the default stays off.
+    const char* wide_env = getenv("YB_C3_WIDE");          // read per plan (tests switch it between plans)
+    const int wm = wide_env ? atoi(wide_env) : 0;
+    if (wm != 0) {
+      const int rcw = conv3w_plan_create(d, wm == 1 ? 1 : 0, &P->wide);
+      if (rcw == YB_OK) { *out = P; return YB_OK; }
+      if (rcw != YB_ERR_UNSUPPORTED) { delete P; return rcw; }
+    }
+  }
   A.bias = d.bias; A.bias_len = d.cout_pad; A.act = d.act; A.slope = d.leaky_slope;
   A.BK = Cin >= 64 ? 64 : 32;
   A.kchunks = (Cin + A.BK - 1) / A.BK;
@@ -413,6 +429,7 @@ int conv3_tc_plan_create(const yb_conv_desc& d, Conv3Plan** out) {
 }
 
 int conv3_tc_launch(const Conv3Plan* P, cudaStream_t s) {
+  if (P->wide) return conv3w_launch(P->wide, s);
   static bool attr_set = false;
   if (!attr_set) {
     YB_CUDA(cudaFuncSetAttribute(k_conv3_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));

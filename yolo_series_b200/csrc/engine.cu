@@ -178,7 +178,7 @@ extern "C" const char* yb_engine_op_kernel(const yb_engine* e, int i) {
   const yb_op& o = e->ops[i];
   switch (o.kind) {
     case YB_OP_CONV:
-      return e->plans_s2p[i] ? "k_conv3s2p_tc" : e->plans3[i] ? "k_conv3_tc" : e->plans[i] ? "k_conv_tc" : "k_conv_fp32";
+      return e->plans_s2p[i] ? "k_conv3s2p_tc" : e->plans3[i] ? conv3_tc_kernel_name(e->plans3[i]) : e->plans[i] ? "k_conv_tc" : "k_conv_fp32";
     case YB_OP_STEM: {
       const yb_tensor& im = e->tensors[o.in0];
       const yb_tensor& y = e->tensors[o.out0];
