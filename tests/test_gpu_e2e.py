@@ -207,7 +207,22 @@ def test_peer_gather_single_rank_equals_detect():
         pg.check()
         with pytest.raises(ValueError):
             pg.begin(8, 50)
-        pg.close()
+        # two batches in flight (bench.py --streams 2 on N > 1 GPUs): one PeerGather per compute stream, because the slot
+        # protocol of a gather is ordered by one stream; a single gather with two compute streams is refused
+        pg2 = ydist.PeerGather(4, 50)
+        xs = [synth_image(4, 96, 128, seed=60 + i, dtype=torch.uint8).pin_memory() for i in range(7)]
+        ref = [m.detect(xb.cuda(), 0.05, 0.5, max_det=50, packed=True) for xb in xs]
+        got = [(o.clone(), c.clone()) for o, c in m.detect_batches(iter(xs), 0.05, 0.5, max_det=50, gather=[pg, pg2],
+                                                                   compute_streams=2)]
+        assert len(got) == len(xs)
+        for (o, c), (wo, wm) in zip(got, ref):
+            assert torch.equal(c, wm[:4].cpu())
+            for i in range(4):
+                assert torch.equal(o[i, :c[i]], wo[i, :c[i]].cpu())
+        with pytest.raises(ValueError):
+            list(m.detect_batches(iter(xs[:1]), 0.05, 0.5, max_det=50, gather=pg, compute_streams=2))
+        pg.check(), pg2.check()
+        pg.close(), pg2.close()
         assert int(want_meta[:4].sum()) > 0
         # a sender that never arrives: the bounded wait must poison its block (counts = -1) and set the status word, and
         # the host-side read-back paths must raise instead of returning stale rows
