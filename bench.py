@@ -258,7 +258,49 @@ def trunk_and_nms_ms(model, eng, reps=10):
     return t_trunk / reps, t_nms / reps, A, head.no
 
 
-def kernel_rooflines(model, eng, peaks, peak_src, traffic_by_kernel, step_ms=None):
+def in_graph_spans(model, x_dev, reps=3):
+    """Per-launch time of the tcgen05 conv kernels INSIDE one replay of the captured trunk graph, from per-CTA
+    %globaltimer stamps the kernels write when a plan was created with YB_CONV_TS set (first griddepcontrol.wait
+    returned -> last CTA exit; csrc/tc_common.cuh YB_CTS, scripts/step_timeline.py).  The eager per-op pass puts an
+    event -- and a full dependency -- between consecutive ops, which inflates the many short launches; these spans
+    are what the launches cost in the graph.  Returns {op index: span ms} (median of `reps` replays) and the engine."""
+    import torch
+    ctas, slots = 320, 16
+    stride = ctas * slots
+    ts = torch.zeros(512 * stride, dtype=torch.int64, device=x_dev.device)
+    os.environ['YB_CONV_TS'], os.environ['YB_CONV_TS_STRIDE'] = hex(ts.data_ptr()), str(stride)
+    try:
+        st = torch.cuda.Stream(x_dev.device)          # engines are cached per stream: this one is built with the stamps on
+        with torch.cuda.stream(st):
+            eng = model.run_trunk(x_dev)
+            for _ in range(2):
+                model.run_trunk(x_dev)
+            stamped = [i for i in range(len(eng.ops)) if eng.op_kernel(i) in
+                       ('k_conv_tc', 'k_conv3_tc', 'k_conv3w_tc', 'k_conv3s2p_tc')]
+            runs = []
+            for _ in range(reps):
+                st.synchronize()
+                ts.zero_()
+                st.synchronize()
+                model.run_trunk(x_dev)
+                st.synchronize()
+                t = ts.view(-1, ctas, slots)[:len(stamped)].cpu()
+                spans = {}
+                for slot, i in enumerate(stamped):
+                    a = t[slot]
+                    a = a[a[:, 0] > 0]
+                    w, ex = a[:, 2][a[:, 2] > 0], a[:, 9][a[:, 9] > 0]
+                    if w.numel() and ex.numel():
+                        spans[i] = (int(ex.max()) - int(w.min())) / 1e6
+                runs.append(spans)
+    finally:
+        os.environ.pop('YB_CONV_TS', None)
+        os.environ.pop('YB_CONV_TS_STRIDE', None)
+    out = {i: sorted(r[i] for r in runs if i in r)[len(runs) // 2] for i in runs[0]}
+    return out, eng, ts
+
+
+def kernel_rooflines(model, eng, peaks, peak_src, traffic_by_kernel, step_ms=None, x_dev=None):
     """One roofline entry per kernel of the step.  Per-op times come from an eager pass with a CUDA event between
     consecutive ops (yb_engine_profile); that pass runs without the graph's programmatic-dependent-launch overlap, so
     its per-kernel SHARES are applied to the measured time of the captured trunk graph -- every `ms` below is a slice
@@ -279,6 +321,17 @@ def kernel_rooflines(model, eng, peaks, peak_src, traffic_by_kernel, step_ms=Non
         tt, th = r['flops'] / (tf_peak * 1e9), r['bytes'] / (hbm_peak * 1e6)
         g['launches'] += 1; g['ms_eager'] += r['ms']; g['flops'] += r['flops']; g['bytes'] += r['bytes']
         g['bound_ms'] += max(tt, th); g['t_tensor'] += tt; g['t_hbm'] += th
+    spans = {}
+    if x_dev is not None:
+        try:
+            spans, _eng2, _ts = in_graph_spans(model, x_dev)
+        except Exception as ex:  # noqa: BLE001
+            print(f'[bench] in-graph spans unavailable: {ex}', file=sys.stderr)
+    for i, r in enumerate(table):
+        if i in spans:
+            g = groups[r['kernel']]
+            g['span_ms'] = g.get('span_ms', 0.0) + spans[i]
+            g['span_bound_ms'] = g.get('span_bound_ms', 0.0) + max(r['flops'] / (tf_peak * 1e9), r['bytes'] / (hbm_peak * 1e6))
     out = []
     for k, g in groups.items():
         ms = g['ms_eager'] * trunk_ms / eager_ms
@@ -289,6 +342,9 @@ def kernel_rooflines(model, eng, peaks, peak_src, traffic_by_kernel, step_ms=Non
                     'frac': ach / (tf_peak if tensor else hbm_peak), 'frac_of_layer_bound': g['bound_ms'] / ms,
                     'tflops': g['flops'] / ms / 1e9, 'algorithmic_GBps': g['bytes'] / ms / 1e6,
                     'flops': g['flops'], 'bytes': g['bytes'], 'traffic': traffic_by_kernel.get(k)})
+        if g.get('span_ms'):      # the same launches inside the graph (timer stamps): see in_graph_spans
+            out[-1]['in_graph_ms'] = round(g['span_ms'], 4)
+            out[-1]['in_graph_frac_of_layer_bound'] = round(g['span_bound_ms'] / g['span_ms'], 4)
     nms_bytes = eng.B * A * no * 4 + eng.B * MAX_DET * 24 + eng.B * 4
     out.append({'kernel': 'k_filter_cells+k_sort_nms', 'launches': 2, 'ms': nms_ms, 'bound': 'hbm',
                 'achieved': nms_bytes / nms_ms / 1e6, 'peak': hbm_peak, 'unit': 'GB/s',
@@ -307,6 +363,10 @@ def kernel_rooflines(model, eng, peaks, peak_src, traffic_by_kernel, step_ms=Non
                'conv_tflops': round(sum(r['flops'] for r in conv) / sum(r['ms'] for r in conv) / 1e9, 1),
                'conv_frac_of_sustained_bf16': round(sum(r['flops'] for r in conv) / sum(r['ms'] for r in conv) / 1e9 / tf_peak, 4),
                'step_frac_of_layer_bounds': round(sum(r['frac_of_layer_bound'] * r['ms'] for r in out) / sum(r['ms'] for r in out), 4),
+               'in_graph': ('in_graph_ms / in_graph_frac_of_layer_bound: the conv launches timed INSIDE a graph replay by per-CTA '
+                            '%globaltimer stamps (first griddepcontrol.wait passed -> last CTA exit, summed per kernel), '
+                            'measured in a separate replay at that moment\'s clocks -- the eager per-op pass serialises '
+                            'consecutive launches and overstates the many short ones'),
                'trunk_graph_ms_alone': round(measured[0], 4), 'decode_nms_ms_alone': round(measured[1], 4),
                'method': ('per-kernel shares of an eager per-op event pass applied to the captured trunk graph; trunk graph '
                           'and decode+NMS are timed alone with CUDA events (.._alone) and scaled so that their sum is the '
@@ -546,12 +606,14 @@ def main():
             traffic_src = os.path.relpath(tp, ROOT) + ' (ncu dram__bytes_read+write summed over the kernel\'s launches of one step)'
         except Exception:  # noqa: BLE001
             pass
-        kernels, summary, table = kernel_rooflines(model, eng, peaks, peak_src, traffic, step_ms=ms_serial / args.steps)
+        kernels, summary, table = kernel_rooflines(model, eng, peaks, peak_src, traffic, step_ms=ms_serial / args.steps, x_dev=x_dev)
         top = dict(kernels[0])
         line['roofline'] = {'bound': top['bound'], 'achieved': top['achieved'], 'peak': top['peak'], 'unit': top['unit'],
                             'frac': top['frac'], 'traffic': top['traffic'], 'kernel': top['kernel'],
                             'launches_per_step': top['launches'], 'ms_per_step': top['ms'],
                             'frac_of_layer_bound': top['frac_of_layer_bound'],
+                            'in_graph_ms': top.get('in_graph_ms'),
+                            'in_graph_frac_of_layer_bound': top.get('in_graph_frac_of_layer_bound'),
                             'peak_source': peak_src + (' (sustained bf16 cuBLAS)' if top['bound'] == 'tensor' else ' (HBM copy)'),
                             'traffic_source': traffic_src, **summary}
         line['roofline_kernels'] = kernels

@@ -13,7 +13,7 @@ print('value', round(d['value'], 1), 'ms/step', round(d['ms_per_step'], 4), 'e2e
 r = d.get('roofline', {})
 print({k: r.get(k) for k in ('kernel', 'bound', 'achieved', 'frac', 'ms_per_step', 'frac_of_layer_bound', 'trunk_graph_ms', 'decode_nms_ms', 'eager_per_op_sum_ms', 'conv_tflops', 'conv_frac_of_sustained_bf16', 'step_frac_of_layer_bounds')})
 for k in d.get('roofline_kernels', []):
-    print(' ', k['kernel'], k['launches'], 'ms', k['ms'], k['bound'], k['achieved'], k['unit'], 'frac', k['frac'], 'of-layer-bound', k['frac_of_layer_bound'])
+    print(' ', k['kernel'], k['launches'], 'ms', k['ms'], k['bound'], k['achieved'], k['unit'], 'frac', k['frac'], 'of-layer-bound', k['frac_of_layer_bound'], '| in graph ms', k.get('in_graph_ms'), 'of-layer-bound', k.get('in_graph_frac_of_layer_bound'))
 ns = d.get('nms_stress') or {}
 print('nms_stress', {k: ns.get(k) for k in ('us_per_image', 'frac_of_hbm_peak', 'cpu_us_per_image', 'cpu_us_per_image_1thread', 'cpu_threads', 'gpu_vs_cpu', 'parity_on_sample', 'error')})
 print('cpu_baseline', d.get('cpu_baseline'))
