@@ -308,7 +308,7 @@ def kernel_rooflines(model, eng, peaks, peak_src, traffic_by_kernel, step_ms=Non
     peak, summed over its launches (per-layer bound); frac = bound time / measured time."""
     trunk_ms, nms_ms, A, no = trunk_and_nms_ms(model, eng)
     measured = (trunk_ms, nms_ms)
-    if step_ms:     # slices of the TIMED one-stream step: the separate trunk / NMS timings run later, on a warmer GPU
+    if step_ms:     # slices of the TIMED step: the separate trunk / NMS timings run later, on a warmer GPU
         sc = step_ms / (trunk_ms + nms_ms)
         trunk_ms, nms_ms = trunk_ms * sc, nms_ms * sc
     table = eng.profile_table(3)
@@ -369,8 +369,9 @@ def kernel_rooflines(model, eng, peaks, peak_src, traffic_by_kernel, step_ms=Non
                             'consecutive launches and overstates the many short ones'),
                'trunk_graph_ms_alone': round(measured[0], 4), 'decode_nms_ms_alone': round(measured[1], 4),
                'method': ('per-kernel shares of an eager per-op event pass applied to the captured trunk graph; trunk graph '
-                          'and decode+NMS are timed alone with CUDA events (.._alone) and scaled so that their sum is the '
-                          'timed one-stream step (ms_per_step_one_stream) -- every ms is a slice of a timed step'),
+                          'and decode+NMS are timed alone with CUDA events (.._alone) and scaled by one factor so that '
+                          'their sum is the timed step (ms_per_step) -- every ms is a slice of the timed step; with two '
+                          'batches in flight that slice is the kernel\'s share of the wall time, its rate an effective one'),
                'peaks': f'{peak_src}: bf16 sustained {tf_peak} TFLOP/s, HBM copy {hbm_peak} GB/s'}
     return out, summary, table
 
@@ -606,7 +607,7 @@ def main():
             traffic_src = os.path.relpath(tp, ROOT) + ' (ncu dram__bytes_read+write summed over the kernel\'s launches of one step)'
         except Exception:  # noqa: BLE001
             pass
-        kernels, summary, table = kernel_rooflines(model, eng, peaks, peak_src, traffic, step_ms=ms_serial / args.steps, x_dev=x_dev)
+        kernels, summary, table = kernel_rooflines(model, eng, peaks, peak_src, traffic, step_ms=ms_dev / args.steps, x_dev=x_dev)
         top = dict(kernels[0])
         line['roofline'] = {'bound': top['bound'], 'achieved': top['achieved'], 'peak': top['peak'], 'unit': top['unit'],
                             'frac': top['frac'], 'traffic': top['traffic'], 'kernel': top['kernel'],
