@@ -40,7 +40,7 @@ struct Conv3wArgs {
   int BN, nsub, kchunks, wstages;
   int act; float slope;
   int tmem_cols, bias_len, total_tiles;
-  uint32_t a_bytes, a_tx;          // slab bytes (1024-aligned, incl. the overrun of the last tap) / bytes TMA delivers
+  uint32_t a_bytes, a_tx;          // slab bytes rounded up to 1024 / bytes TMA delivers
   uint32_t idesc;
   unsigned long long* dbg;
 };
