@@ -1,48 +1,42 @@
-"""Where the time of Model.detect(augment=True) goes (yolov7 640 B=32 bf16): CUDA events per stage."""
+"""Where the time of Model.forward(augment=True) + NMS goes (yolo.py:582-597): per pass scale_img, trunk, decode; then NMS."""
 import os
 import sys
 
-import torch
-
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from yolo_series_b200 import Model, _lib                                  # noqa: E402
-from yolo_series_b200.nms import _run_nms                                 # noqa: E402
-from yolo_series_b200.synth import seeded_state_dict, synth_image        # noqa: E402
+import torch  # noqa: E402
 
+from yolo_series_b200 import Model, non_max_suppression  # noqa: E402
+from yolo_series_b200.synth import seeded_state_dict, synth_image  # noqa: E402
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
 m = Model('yolov7')
 m.load_state_dict(seeded_state_dict(m, 0))
 m = m.cuda().eval().half()
-B = 32
 x = synth_image(B, 640, 640, seed=1, dtype=torch.uint8).cuda()
 
 
-def t(fn, n=10):
+def timed(fn, reps=10):
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(n):
-        fn()
-    b.record()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        out = fn()
+    e1.record()
     torch.cuda.synchronize()
-    return a.elapsed_time(b) / n
+    return e0.elapsed_time(e1) / reps, out
 
 
-passes = m._passes(640, 640, True)
-print('passes', passes)
-xs = []
-for si, fi, hw, HW in passes:
-    xi = x if si == 1 else m._scaled_input(x, si, fi, hw, HW)
-    xs.append(xi)
-    if si != 1:
-        print(f'scale_img {si}: {t(lambda: m._scaled_input(x, si, fi, hw, HW)):.3f} ms')
-    print(f'trunk {HW} ({xi.dtype}): {t(lambda: m.run_trunk(xi)):.3f} ms')
-    xu = synth_image(B, HW[0], HW[1], seed=1, dtype=torch.uint8).cuda()
-    print(f'trunk {HW} (uint8 input): {t(lambda: m.run_trunk(xu)):.3f} ms')
-pred = m(x, augment=True)[0]
-print('pred', tuple(pred.shape))
-print(f'forward(augment) total: {t(lambda: m(x, augment=True)):.3f} ms')
-print(f'nms on TTA pred: {t(lambda: _run_nms(pred, B, pred.shape[1], 85, 0.001, 0.65, None, False, False, 30000, 300, pred.device, return_packed=True)):.3f} ms')
-print(f'detect(augment) total: {t(lambda: m.detect(x, 0.001, 0.65, augment=True, packed=True)):.3f} ms')
-print(f'detect plain: {t(lambda: m.detect(x, 0.001, 0.65, packed=True)):.3f} ms')
+t_plain, _ = timed(lambda: m.detect(x, 0.001, 0.65, packed=True))
+t_fwd, pa = timed(lambda: m(x, augment=True)[0])
+t_all, _ = timed(lambda: m.detect(x, 0.001, 0.65, packed=True, augment=True))
+print(f'plain step {t_plain:.3f} ms; TTA forward (3 passes -> pred {tuple(pa.shape)}) {t_fwd:.3f} ms; TTA forward + NMS {t_all:.3f} ms')
+H = W = 640
+for si, fi, hw, HW in m._passes(H, W, True):
+    xi = x if (si == 1.0 and not fi) else m._scaled_input(x, si, fi, hw, HW)
+    t_s, _ = timed(lambda: None if (si == 1.0 and not fi) else m._scaled_input(x, si, fi, hw, HW))
+    t_t, eng = timed(lambda: m.run_trunk(xi))
+    print(f'  pass scale {si} flip {fi} -> {HW}: scale_img {t_s:.3f} ms, trunk {t_t:.3f} ms ({eng.conv_flops / t_t / 1e9:.0f} TFLOP/s)')
+t_n, _ = timed(lambda: non_max_suppression(pa, 0.001, 0.65))
+print(f'  stand-alone NMS on {pa.shape[1]} rows/image (list form, one host sync): {t_n:.3f} ms')
