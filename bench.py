@@ -517,7 +517,7 @@ def main():
                                          compute_streams=n_streams):
             pass
         return last
-    run_stream(3)
+    run_stream(8)          # every slot of the pipeline (six with two compute streams) has been through one batch
     barrier()
     e0.record()
     res, cnt = run_stream(args.steps)

@@ -486,10 +486,20 @@ class Model(nn.Module):
         if compute_streams not in (1, 2) or (gathers[0] is not None and len(gathers) < compute_streams):
             raise ValueError('compute_streams must be 1 or 2, with one PeerGather per compute stream')
         cstreams = [main] if compute_streams == 1 else self.compute_streams(2, dev)
-        h2d, d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
-        slots = [dict(stage=None, host=None, consumed=torch.cuda.Event(), loaded=torch.cuda.Event(),
-                      done=torch.cuda.Event(), read=torch.cuda.Event(), used=False, gather=None)
-                 for _ in range(2 if compute_streams == 1 else 6)]
+        # copy streams, staging buffers and pinned result buffers live with the model: pinning host memory costs
+        # milliseconds, which a fresh set per call would put into every short run (one generator per model at a time)
+        cache = self.__dict__.setdefault('_stream_slots', {})
+        key = (str(dev), compute_streams)
+        if key not in cache:
+            cache[key] = dict(h2d=torch.cuda.Stream(dev), d2h=torch.cuda.Stream(dev),
+                              slots=[dict(stage=None, host=None, consumed=torch.cuda.Event(), loaded=torch.cuda.Event(),
+                                          done=torch.cuda.Event(), read=torch.cuda.Event(), used=False, gather=None)
+                                     for _ in range(2 if compute_streams == 1 else 6)])
+        h2d, d2h, slots = cache[key]['h2d'], cache[key]['d2h'], cache[key]['slots']
+        for s in slots:                      # a previous generator that was abandoned half way may have left work behind
+            if s['used']:
+                s['read'].synchronize()
+            s['keep'] = None
         pending = deque()
 
         def finish(s):
