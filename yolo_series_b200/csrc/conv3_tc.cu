@@ -220,8 +220,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
     const int row = q * 32 + lane;
     const uint32_t xr = (uint32_t)(row & 7);
     const int nchunks = G.BN / 32;
-    const int c_begin = half * ((nchunks + 1) / 2);
-    const int c_end = half == 0 ? (nchunks + 1) / 2 : nchunks;
     const bool store_thread = (warp == 2 && lane == 0);
     int it = 0;
     for (int t = walker; t < G.total_tiles; t += walkers, ++it) {
@@ -233,6 +231,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
       m_tile -= img * tiles_m_per_img;
       const int th = fd_div(m_tile, G.fd_w), tw = m_tile - th * G.tiles_w;
       const int n0 = n_tile * G.BN, w0 = tw * G.BW, h0 = th * G.nsub * G.BH;
+      // only the 32-column chunks that hold real output channels (the last N tile of Cout = 192, 320, ...)
+      const int valid_cols = min(G.BN, G.bias_len - n0);
+      const int nch = min(nchunks, (valid_cols + 31) >> 5);
+      const int c_begin = half * ((nch + 1) / 2);
+      const int c_end = half == 0 ? (nch + 1) / 2 : nch;
       mbar_wait(bar_tfull0 + 8u * par, aph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       for (int j = 0; j < G.nsub; ++j) {
@@ -248,7 +251,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
             if (PAIR && !leader) mbar_arrive_remote(bar_tempty0 + 8u * par, 0u);
             else mbar_arrive(bar_tempty0 + 8u * par);
           }
-          const int ngroups = (G.BN + 63) / 64;
+          const int ngroups = (valid_cols + 63) / 64;
           for (int g = 0; g < ngroups; ++g)
             tma_store_4d(&G.tm_y, staging + (uint32_t)g * 16384u, n0 + g * 64, w0, h0 + j * G.BH, img);
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");

@@ -325,7 +325,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
               rpix = G.res_ptr + (((long long)img * G.out_h + hh) * G.out_w + ww) * G.res_cs;
           }
         }
-        for (int cc = c_first; cc < nchunks; cc += c_step) {
+        // 32-column chunks that hold real output channels: the last N tile of a Cout that is not a multiple of the tile
+        // (160, 320, 480 ... in the P6 cfgs) skips the TMEM reads, the activation math and the staging of the rest
+        const int valid_cols = min(G.BN, G.bias_len - n0);
+        const int nch = min(nchunks, (valid_cols + 31) >> 5);
+        for (int cc = c_first; cc < nch; cc += c_step) {
           uint32_t v[32];
           if (G.res_ptr) {   // loads issued before the TMEM wait so that their latency overlaps it
             uint4 res[4];
@@ -353,7 +357,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
           if (PAIR && !leader) mbar_arrive_remote(bar_tempty0 + 8u * acc, 0u);
           else mbar_arrive(bar_tempty0 + 8u * acc);
           const int per_group = G.out_f32 ? 32 : 64;
-          const int ngroups = (G.BN + per_group - 1) / per_group;
+          const int ngroups = (valid_cols + per_group - 1) / per_group;
           for (int mp = 0; mp < G.n_store_maps; ++mp)
             for (int g = 0; g < ngroups; ++g)
               tma_store_4d(&G.tm_y[mp], sbase + (uint32_t)g * 16384u, n0 + g * per_group, w0, G.flat ? 0 : h0, img);
@@ -493,7 +497,7 @@ static void pick_tile(int cout, long long m_tiles, int chunks, int bk, int y_es,
         const double mma = chunks * (bk / 16) * (bn / 2.0);
         const double a_b = 128.0 * bk * 2, b_b = (double)bn_cta * bk * 2;
         const double load = chunks * (a_b + (res ? 0.0 : b_b)) / 42.0;
-        const double epi = bn * 10.0 + 600.0;
+        const double epi = ((double)cout / tiles_n < bn ? (double)cout / tiles_n : bn) * 10.0 + 600.0;   // chunks past Cout are skipped
         double tile = mma > load ? mma : load;
         if (epi > tile) tile = epi;
         // pairs: cluster launch / cross-CTA handshakes cost a little per tile and at start-up
