@@ -190,6 +190,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
       else mbar_wait(bar_tempty0 + 8u * par, aph ^ 1u);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t tmem_d0 = tmem_base + (par * 2u) * (uint32_t)G.BN;
+      uint32_t idesc = G.idesc;      // last N tile of Cout = 192, 320, ...: only the columns that exist (see k_conv_tc)
+      if (!PAIR) {
+        const int n_tile_m = t - fd_div(t, G.fd_n) * G.tiles_n;
+        const int n_valid = min(G.BN, (G.bias_len - n_tile_m * G.BN + 15) & ~15);
+        idesc = (idesc & ~(0x3Fu << 17)) | ((uint32_t)(n_valid >> 3) << 17);
+      }
       for (int c = 0; c < stages_per_tile; ++c) {
         mbar_wait(bar_full0 + 8u * s, ph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -197,11 +203,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv3_tc(const __grid_constan
         if (elect_one()) {
           const uint32_t acc0 = (uint32_t)(c != 0);
           if (G.nsub == 2) {
-            if (nk == 4) issue_stage<4, 2, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
-            else         issue_stage<2, 2, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+            if (nk == 4) issue_stage<4, 2, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, idesc, acc0);
+            else         issue_stage<2, 2, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, idesc, acc0);
           } else {
-            if (nk == 4) issue_stage<4, 1, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
-            else         issue_stage<2, 1, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, G.idesc, acc0);
+            if (nk == 4) issue_stage<4, 1, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, idesc, acc0);
+            else         issue_stage<2, 1, PAIR>(tmem_d0, (uint32_t)G.BN, dlo, hi32, aoff, boff, idesc, acc0);
           }
           if (PAIR) umma_commit_2sm(bar_empty0 + 8u * s); else umma_commit(bar_empty0 + 8u * s);
         }

@@ -230,6 +230,15 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
       else mbar_wait(bar_tempty0 + 8u * acc, aph ^ 1u);  // epilogue has drained this accumulator
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t tmem_d = tmem_base + acc * (uint32_t)G.BN;
+      // N of this tile's MMAs: the last N tile of a Cout that is not a multiple of BN (320 = 256 + 64 ...) only computes
+      // the columns that exist, rounded up to the instruction's granularity of 16 (single-CTA form; a pair splits the
+      // weight rows between its CTAs by BN / 2, so it keeps the full N)
+      uint32_t idesc = G.idesc;
+      if (!PAIR) {
+        const int n_tile_m = G.resident ? res_n : t - fd_div(t, G.fd_n) * G.tiles_n;
+        const int n_valid = min(G.BN, (G.bias_len - n_tile_m * G.BN + 15) & ~15);
+        idesc = (idesc & ~(0x3Fu << 17)) | ((uint32_t)(n_valid >> 3) << 17);
+      }
       for (int c = 0; c < total_chunks; ++c) {
         mbar_wait(bar_full0 + 8u * s, ph);
         YB_CTS(4, lane == 0 && it == 0 && c == 0);
@@ -252,12 +261,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) k_conv_tc(const __grid_constant
           } else {
           if (nk == 4) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16_lh(tmem_d, da + 2u * k, db + 2u * k, hi32, G.idesc, k ? 1u : acc0);
+            for (int k = 0; k < 4; ++k) umma_bf16_lh(tmem_d, da + 2u * k, db + 2u * k, hi32, idesc, k ? 1u : acc0);
           } else if (nk == 2) {
 #pragma unroll
-            for (int k = 0; k < 2; ++k) umma_bf16_lh(tmem_d, da + 2u * k, db + 2u * k, hi32, G.idesc, k ? 1u : acc0);
+            for (int k = 0; k < 2; ++k) umma_bf16_lh(tmem_d, da + 2u * k, db + 2u * k, hi32, idesc, k ? 1u : acc0);
           } else {
-            umma_bf16_lh(tmem_d, da, db, hi32, G.idesc, acc0);
+            umma_bf16_lh(tmem_d, da, db, hi32, idesc, acc0);
           }
           umma_commit(bar_empty0 + 8u * s);   // frees the smem stage once these MMAs retire
           }
