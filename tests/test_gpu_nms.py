@@ -128,6 +128,34 @@ def test_nms_edge_cases():
     assert got[0].shape[0] == 1 and float(got[0][0, 5]) == 3.0
 
 
+def test_nms_non_finite_boxes_follow_the_reference():
+    """Rows whose box coordinates are NaN / inf but whose scores pass the filter (a NaN box logit next to healthy
+    obj / class logits): torchvision's kernel uses std::max / std::min (first operand on an unordered compare), the CUDA
+    kernel IEEE maxNum / minNum -- the intermediate overlaps differ, but a NaN coordinate makes that box's area and
+    hence every IoU it takes part in NaN, `NaN > thr` is false either way: such a row neither suppresses nor is
+    suppressed.  The kept rows must equal the oracle's, NaN for NaN."""
+    from yolo_series_b200 import non_max_suppression
+    pred = synth_pred(3, 3000, 80, seed=17, p_obj=0.4, clusters=(20, 40))
+    g = torch.Generator().manual_seed(1)
+    for b in range(3):
+        idx = torch.randperm(3000, generator=g)[:60]
+        pred[b, idx[:15], 0] = float('nan')          # x centre
+        pred[b, idx[15:30], 3] = float('nan')        # height
+        pred[b, idx[30:40], 2] = float('inf')        # width: x1 = -inf, x2 = +inf, area inf, IoU = NaN or 0
+        pred[b, idx[40:50], 1] = float('-inf')       # y centre
+        pred[b, idx[50:60], :4] = float('nan')
+        pred[b, idx, 4] = 0.9                        # they all pass the filter and rank high
+    for kw in (dict(conf_thres=0.25, iou_thres=0.45), dict(conf_thres=0.001, iou_thres=0.65, multi_label=True),
+               dict(conf_thres=0.25, iou_thres=0.45, agnostic=True)):
+        ref = non_max_suppression_ref(pred, **kw)
+        got = non_max_suppression(pred.cuda(), **kw)
+        assert [r.shape[0] for r in ref] == [t.shape[0] for t in got], kw
+        a, r = _flat(got), _flat(ref)
+        assert np.array_equal(a, r, equal_nan=True), kw      # NaN payload bits differ between the CPU and the GPU
+        assert np.array_equal(np.isnan(a), np.isnan(r)) and np.array_equal(np.isinf(a), np.isinf(r))
+        assert np.isnan(a).any()                      # not vacuous: non-finite rows are among the kept ones
+
+
 def test_decode_matches_torch_and_fused_path():
     """decode: <= 2 ulp from the CPU sigmoid path; fused decode+NMS == decode -> NMS."""
     from yolo_series_b200 import ops
