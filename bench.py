@@ -384,8 +384,8 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--batch', type=int, default=BATCH, help='images per GPU per step')
     ap.add_argument('--no-extras', action='store_true', help='skip cpu_baseline / NMS stress / per-op profile')
-    ap.add_argument('--streams', type=int, default=2, choices=[1, 2],
-                    help='batches in flight on one GPU: 2 = consecutive steps alternate between two streams / engines')
+    ap.add_argument('--streams', type=int, default=2, choices=[1, 2, 3, 4],
+                    help='batches in flight on one GPU: n = consecutive steps rotate over n streams / engines')
     # secondary BASELINE.json configs (configs[2], configs[3]); the defaults are the headline workload
     ap.add_argument('--model', default=MODEL, help='cfg name (yolov7 | yolov7-tiny | yolov7-w6-custom | yolov7-e6e)')
     ap.add_argument('--img', type=int, default=IMG)
@@ -426,13 +426,13 @@ def main():
     # N > 1: the one exchange of the path (every rank's detections to every rank) happens inside the NMS kernel through
     # peer-to-peer stores over NVLink (dist.PeerGather); YB_GATHER=nccl selects the plain NCCL all-gather instead.
     use_peer = world > 1 and os.environ.get('YB_GATHER', 'peer') != 'nccl'
-    pg = pg2 = None
+    pg, pgs = None, [None] * args.streams
     if use_peer:
-        try:
-            pg = ydist.PeerGather(B, MAX_DET, device=dev)
-            pg2 = ydist.PeerGather(B, MAX_DET, device=dev)     # one per compute stream (its slot protocol is per stream)
+        try:                                # one gather per compute stream (its slot protocol is ordered by one stream)
+            pgs = [ydist.PeerGather(B, MAX_DET, device=dev) for _ in range(args.streams)]
+            pg = pgs[0]
         except RuntimeError as ex:          # raised on every rank together: CUDA IPC unavailable -> NCCL all-gather
-            use_peer, pg, pg2 = False, None, None
+            use_peer, pg, pgs = False, None, [None] * args.streams
             if rank == 0:
                 print(f'[bench] {ex}', file=sys.stderr)
     # Two batches in flight (args.streams = 2): consecutive steps are independent, so step k+1 runs on a second stream
@@ -440,7 +440,6 @@ def main():
     # launches, the 32-CTA NMS).  Every step is still one full pass over one batch; --streams 1 = strictly serial.
     n_streams = args.streams if (world == 1 or use_peer) else 1
     side = model.compute_streams(n_streams, dev) if n_streams > 1 else None
-    pgs = [pg, pg2]
 
     def step_device(k=0, serial=False):
         if side is None or serial:
@@ -513,11 +512,11 @@ def main():
     def run_stream(n):
         last = None
         for last in model.detect_batches((x_host for _ in range(n)), CONF, IOU, max_det=MAX_DET, post=post,
-                                         gather=(pgs if (pg is not None and n_streams == 2) else pg),
+                                         gather=(pgs if (pg is not None and n_streams > 1) else pg),
                                          compute_streams=n_streams):
             pass
         return last
-    run_stream(8)          # every slot of the pipeline (six with two compute streams) has been through one batch
+    run_stream(3 * n_streams + 2)   # every slot of the pipeline (3 per compute stream) has been through one batch
     barrier()
     e0.record()
     res, cnt = run_stream(args.steps)
@@ -553,7 +552,7 @@ def main():
             gather_check = 'bit-identical' if ok else 'MISMATCH'
         barrier()
     if pg is not None:
-        for g in (pg, pg2):
+        for g in pgs:
             g.check()
             g.close()
     if rank != 0:
@@ -583,7 +582,7 @@ def main():
                    'input': 'one seeded pinned uint8 batch per rank, re-sent H2D every e2e step'},
         'e2e': {'value': n_imgs / (ms_e2e / 1e3), 'unit': 'images/s', 'h2d_bytes_per_step': x_host.numel(),
                 'd2h_bytes_per_step': int(res.numel() * 4 + cnt.numel() * 4 + 4), 'ms_per_step': ms_e2e / args.steps,
-                'api': f'Model.detect_batches (H2D / D2H copy streams + {n_streams} compute stream(s), {2 if n_streams == 1 else 6} slots)',
+                'api': f'Model.detect_batches (H2D / D2H copy streams + {n_streams} compute stream(s), {2 if n_streams == 1 else 3 * n_streams} slots)',
                 'serial_value': n_imgs / (ms_e2e_serial / 1e3),
                 'serial_api': 'Model.detect(x_host) + .cpu() per step, one stream'},
         'gpu_launches': launches_per_step * args.steps,

@@ -465,7 +465,8 @@ class Model(nn.Module):
         Copy streams and slots: batch i+1's H2D copy and batch i-1's D2H read run on their own copy streams
         while batch i computes, so PCIe time leaves the critical path; each step still moves its own input H2D and its
         own result D2H.  ``compute_streams`` = 2 (the default without ``post`` / with no or two ``gather`` objects)
-        alternates the batches between two side streams with one engine each and six slots: consecutive batches are
+        alternates the batches between two side streams with one engine each and six slots (3 or 4 streams: 9 / 12 slots;
+        they only pay at very small batches -- batch 1: 0.49 ms per image with two, 0.39 with three): consecutive batches are
         independent, so the CTAs of batch i+1 fill the SMs that batch i's persistent kernels leave idle in their last
         round and between dependent launches -- +2.4 % images/s at batch 32 (`scripts/e2e_streams_probe.py`; two or
         three slots are too shallow: the host then enqueues a batch only when both streams are about to drain), ~+60 %
@@ -483,9 +484,9 @@ class Model(nn.Module):
         gathers = list(gather) if isinstance(gather, (list, tuple)) else [gather]
         if compute_streams is None:      # a PeerGather's slot protocol is ordered by ONE stream: one gather per stream
             compute_streams = 2 if (post is None and (gather is None or len(gathers) == 2)) else 1
-        if compute_streams not in (1, 2) or (gathers[0] is not None and len(gathers) < compute_streams):
-            raise ValueError('compute_streams must be 1 or 2, with one PeerGather per compute stream')
-        cstreams = [main] if compute_streams == 1 else self.compute_streams(2, dev)
+        if compute_streams not in (1, 2, 3, 4) or (gathers[0] is not None and len(gathers) < compute_streams):
+            raise ValueError('compute_streams must be 1..4, with one PeerGather per compute stream')
+        cstreams = [main] if compute_streams == 1 else self.compute_streams(compute_streams, dev)
         # copy streams, staging buffers and pinned result buffers live with the model: pinning host memory costs
         # milliseconds, which a fresh set per call would put into every short run (one generator per model at a time)
         cache = self.__dict__.setdefault('_stream_slots', {})
@@ -494,7 +495,7 @@ class Model(nn.Module):
             cache[key] = dict(h2d=torch.cuda.Stream(dev), d2h=torch.cuda.Stream(dev),
                               slots=[dict(stage=None, host=None, consumed=torch.cuda.Event(), loaded=torch.cuda.Event(),
                                           done=torch.cuda.Event(), read=torch.cuda.Event(), used=False, gather=None)
-                                     for _ in range(2 if compute_streams == 1 else 6)])
+                                     for _ in range(2 if compute_streams == 1 else 3 * compute_streams)])
         h2d, d2h, slots = cache[key]['h2d'], cache[key]['d2h'], cache[key]['slots']
         for s in slots:                      # a previous generator that was abandoned half way may have left work behind
             if s['used']:
@@ -524,8 +525,8 @@ class Model(nn.Module):
             with torch.cuda.stream(h2d):
                 s['stage'].copy_(xb, non_blocking=True)
                 s['loaded'].record(h2d)
-            cs = cstreams[(i & 1) % len(cstreams)]
-            g = gathers[(i & 1) % len(gathers)]
+            cs = cstreams[i % len(cstreams)]
+            g = gathers[i % len(cstreams)] if len(gathers) > 1 else gathers[0]
             cs.wait_event(s['loaded'])
             if s['used']:
                 cs.wait_event(s['read'])         # the slot's previous result has left the device
