@@ -217,3 +217,31 @@ def test_ensemble_and_eval_surface_without_gpu():
         evaluate.match_batch(torch.zeros(1, 4, 6), torch.zeros(1, dtype=torch.int32), torch.zeros(0, 6), (64, 64),
                              [dict(shape0=(64, 64), ratio=(1, 1), pad=(0, 0))], torch.linspace(0.5, 0.95, 10))
     assert evaluate.NMS.conf == 0.25 and evaluate.NMS.iou == 0.45 and evaluate.autoShape.classes is None
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` (the reference algorithm on the host cores, the driver's denominator): ONE JSON line with
+    the same metric string the b200 arm prints for that workload, `impl`, a `cpu_baseline` describing the run and an
+    `e2e` object without copies.  Runs on the CPU (small cfg / size so that it takes seconds)."""
+    import json
+    import os
+    import subprocess
+    import sys
+
+    import bench
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, os.path.join(root, 'bench.py'), '--impl', 'reference', '--model', 'yolov7-tiny',
+                        '--img', '320', '--steps', '1', '--warmup', '0'], capture_output=True, text=True, timeout=600, cwd=root)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [ln for ln in p.stdout.strip().splitlines() if ln.startswith('{')]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d['impl'] == 'reference' and d['metric'] == bench.metric_name('yolov7-tiny', 320)
+    for k in ('value', 'unit', 'n_gpus', 'steps', 'warmup', 'ms_per_step', 'higher_is_better', 'scaling', 'vs_baseline',
+              'dtype', 'data', 'config', 'cpu_baseline', 'e2e', 'gpu_launches'):
+        assert k in d, k
+    assert d['unit'] == 'images/s' and d['higher_is_better'] is True and d['vs_baseline'] is None and d['n_gpus'] == 1
+    assert d['value'] > 0 and d['gpu_launches'] == 0 and 'workload' in d['config']
+    cb, e = d['cpu_baseline'], d['e2e']
+    assert cb['kind'] == 'port' and cb['cores'] >= 1 and cb['value'] == d['value'] and 'sample' in cb
+    assert e['value'] == d['value'] and e['unit'] == d['unit'] and e['h2d_bytes_per_step'] == 0 and e['d2h_bytes_per_step'] == 0
