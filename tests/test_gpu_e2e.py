@@ -286,3 +286,30 @@ def test_forward_profile_prints_per_op_table(capsys):
     assert torch.equal(a, b)
     txt = capsys.readouterr().out
     assert 'k_conv' in txt and 'ms total' in txt
+
+
+def test_bench_line_contract_no_extras():
+    """`bench.py` (b200 arm) on a small workload: ONE JSON line with the contract keys, the metric string shared with the
+    reference arm, e2e with its copy sizes, the clocks sample and the in-flight configuration."""
+    import json
+    import os
+    import subprocess
+    import sys
+
+    import bench
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, os.path.join(root, 'bench.py'), '--model', 'yolov7-tiny', '--img', '320', '--batch', '4',
+                        '--steps', '5', '--warmup', '3', '--no-extras'], capture_output=True, text=True, timeout=600, cwd=root)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [ln for ln in p.stdout.strip().splitlines() if ln.startswith('{')]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d['metric'] == bench.metric_name('yolov7-tiny', 320) and 'impl' not in d
+    for k in ('value', 'unit', 'n_gpus', 'steps', 'warmup', 'ms_per_step', 'higher_is_better', 'scaling', 'vs_baseline',
+              'dtype', 'data', 'config', 'e2e', 'gpu_launches', 'clocks', 'value_one_stream'):
+        assert k in d, k
+    assert d['steps'] == 5 and d['n_gpus'] == 1 and d['dtype'] == 'bf16' and d['scaling'] == 'weak'
+    assert d['value'] > 0 and d['gpu_launches'] > 0 and d['config']['streams'] == 2
+    e = d['e2e']
+    assert e['value'] > 0 and e['h2d_bytes_per_step'] == 4 * 3 * 320 * 320 and e['d2h_bytes_per_step'] > 0
+    assert abs(d['value'] - 4 * 5 / (d['ms_per_step'] * 5 / 1e3)) / d['value'] < 1e-6
