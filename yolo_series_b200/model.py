@@ -475,7 +475,7 @@ class Model(nn.Module):
         ``post(out, counts) -> (out, counts)`` runs on the compute stream before the read-back (e.g.
         ``dist.gather_detections``); ``gather`` (a ``dist.PeerGather``, or one per compute stream) does the multi-GPU
         exchange inside the NMS kernel instead and every yielded pair then covers the global batch.  A yielded pair
-        stays valid until the next batch is drawn (its pinned buffers are reused two -- or six -- batches later)."""
+        stays valid until the next batch is drawn (its pinned buffers are reused once every slot has been used again: 2 batches later with one compute stream, 3 per stream otherwise)."""
         from collections import deque
         dev = self._device()
         if dev.type != 'cuda':
